@@ -1,0 +1,152 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_core.hpp header).
+// C entry points for ctypes (tests/, smoke(), bench.py cpu_baseline / --impl reference).
+#include "hanging_chain.hpp"
+#include "oracle_alm.hpp"
+#include <atomic>
+#include <cstring>
+#include <memory>
+#include <thread>
+
+using namespace oracle;
+
+namespace {
+
+constexpr int NPARAMS = 48, NSTATS = 24;
+
+std::unique_ptr<Problem> make_problem(int problem_id, int N) {
+    switch (problem_id) {
+        case 0: return std::make_unique<HangingChain>(N);
+        default: return nullptr;
+    }
+}
+int nx_of(int problem_id) { return problem_id == 0 ? HangingChain::NX : 9; }
+void set_x0(Problem &p, int problem_id, const double *x0) {
+    if (problem_id == 0) { auto &hc = static_cast<HangingChain &>(p); std::copy(x0, x0 + hc.NX, hc.x0.begin()); }
+}
+
+ALMSolver make_solver(const double *P) {
+    ALMSolver s;
+    auto &a = s.params;
+    a.tolerance = P[0]; a.dual_tolerance = P[1]; a.penalty_update_factor = P[2];
+    a.initial_penalty = P[3]; a.initial_tolerance = P[4]; a.tolerance_update_factor = P[5];
+    a.rel_penalty_increase_threshold = P[6]; a.max_multiplier = P[7]; a.max_penalty = P[8];
+    a.min_penalty = P[9]; a.max_iter = (unsigned)P[10]; a.initial_penalty_factor = P[11];
+    a.single_penalty_factor = P[12] != 0;
+    auto &p = s.inner_solver.params;
+    p.max_iter = (unsigned)P[16]; p.stop_crit = (int)P[17]; p.L_min = P[18]; p.L_max = P[19];
+    p.quadratic_upperbound_tolerance_factor = P[20]; p.TR_tolerance_factor = P[21];
+    p.ratio_threshold_acceptable = P[22]; p.ratio_threshold_good = P[23];
+    p.radius_factor_rejected = P[24]; p.radius_factor_acceptable = P[25]; p.radius_factor_good = P[26];
+    p.initial_radius = P[27]; p.min_radius = P[28];
+    p.Lipschitz.L_0 = P[29]; p.Lipschitz.eps = P[30]; p.Lipschitz.delta = P[31];
+    p.Lipschitz.Lgamma_factor = P[32];
+    p.compute_ratio_using_new_stepsize = P[33] != 0;
+    p.recompute_last_prox_step_after_direction_reset = P[34] != 0;
+    p.disable_acceleration = P[35] != 0; p.ratio_approx_fbe_quadratic_model = P[36] != 0;
+    s.inner_solver.direction.direction_params.hessian_vec_factor = P[40];
+    auto &c = s.inner_solver.direction.steihaug.params;
+    c.tol_scale = P[44]; c.tol_scale_root = P[45]; c.tol_max = P[46]; c.max_iter_factor = P[47];
+    return s;
+}
+
+void write_stats(const ALMStats &s, const EvalCounter &e, double *o) {
+    o[0] = s.status; o[1] = s.outer_iterations; o[2] = s.inner_iterations; o[3] = s.eps_;
+    o[4] = s.delta; o[5] = s.norm_penalty; o[6] = s.final_psi; o[7] = s.final_gamma;
+    o[8] = s.final_fbe; o[9] = s.accelerated_step_rejected; o[10] = s.direction_failures;
+    o[11] = s.inner_convergence_failures; o[12] = e.psi; o[13] = e.psi_grad_psi; o[14] = e.grad_L;
+    o[15] = e.hess_psi_prod; o[16] = e.prox_grad_step; o[17] = e.grad_psi;
+    o[18] = e.inactive_indices_res_lna; o[19] = e.proj_multipliers; o[20] = o[21] = o[22] = o[23] = 0;
+}
+
+} // namespace
+
+extern "C" {
+
+int oracle_nparams() { return NPARAMS; }
+int oracle_nstats() { return NSTATS; }
+int oracle_trace_width() { return 11; }
+
+// dims[0..3] = n, m, nx, nu
+int oracle_dims(int problem_id, int N, long *dims) {
+    auto p = make_problem(problem_id, N);
+    if (!p) return -1;
+    dims[0] = p->n; dims[1] = p->m; dims[2] = nx_of(problem_id); dims[3] = p->n / N;
+    return 0;
+}
+
+// Evaluate psi, grad psi, yhat and (if v) hess_psi_prod at (u, y, Sigma) for initial state x0.
+int oracle_eval(int problem_id, int N, const double *x0, const double *u, const double *y,
+                const double *Sigma, const double *v, double *psi, double *grad, double *yhat,
+                double *Hv) {
+    auto p = make_problem(problem_id, N);
+    if (!p) return -1;
+    set_x0(*p, problem_id, x0);
+    if (grad) *psi = p->eval_psi_grad_psi(u, y, Sigma, grad);
+    if (yhat || !grad) *psi = p->eval_psi(u, y, Sigma, yhat);
+    if (v && Hv) p->eval_hess_psi_prod(u, y, Sigma, 1, v, Hv);
+    return 0;
+}
+
+// Plant step x+ = f_d(x, u): problems/problems/formulation.hpp:258-261
+int oracle_simulate_dynamics(int problem_id, const double *x, const double *u, double *xn) {
+    if (problem_id != 0) return -1;
+    HangingChain hc(1);
+    hc.rk4(x, u, xn);
+    return 0;
+}
+
+// One ALM+PANTR solve.  u (n) and y (m) are in/out.  trace (optional): max_trace rows of 11 doubles.
+int oracle_solve(int problem_id, int N, const double *params, const double *x0, double *u, double *y,
+                 double *stats, double *trace, int max_trace, int *n_trace) {
+    auto p = make_problem(problem_id, N);
+    if (!p) return -1;
+    set_x0(*p, problem_id, x0);
+    auto solver = make_solver(params);
+    std::vector<TraceRec> tr;
+    if (trace) solver.inner_solver.trace = &tr;
+    vec x(u, u + p->n), yy(y, y + p->m);
+    auto s = solver(*p, x, yy);
+    std::copy(x.begin(), x.end(), u);
+    std::copy(yy.begin(), yy.end(), y);
+    write_stats(s, p->evaluations, stats);
+    if (trace) {
+        int nt = std::min<int>(max_trace, (int)tr.size());
+        for (int i = 0; i < nt; ++i) {
+            double *r = trace + 11 * i; const auto &t = tr[i];
+            r[0] = t.k; r[1] = t.psi; r[2] = t.fbe; r[3] = t.gamma; r[4] = t.eps_; r[5] = t.radius;
+            r[6] = t.rho; r[7] = t.q_model; r[8] = t.nJ; r[9] = t.cg_iters; r[10] = t.accepted;
+        }
+        if (n_trace) *n_trace = (int)tr.size();
+    }
+    return 0;
+}
+
+// B independent solves, one instance per thread at a time (the reference runs one process per
+// experiment: new-benchmarks-paper/run-single-mpc-exp.sh:19, README.md:19).
+int oracle_solve_batch(int problem_id, int N, const double *params, long B, const double *x0,
+                       double *u, double *y, double *stats, int nthreads) {
+    auto probe = make_problem(problem_id, N);
+    if (!probe) return -1;
+    const long n = probe->n, m = probe->m, nx = nx_of(problem_id);
+    std::atomic<long> next{0};
+    auto worker = [&] {
+        auto p = make_problem(problem_id, N);
+        auto solver = make_solver(params);
+        for (long b; (b = next.fetch_add(1)) < B;) {
+            set_x0(*p, problem_id, x0 + b * nx);
+            p->evaluations = {};
+            vec x(u + b * n, u + (b + 1) * n), yy(y + b * m, y + (b + 1) * m);
+            auto s = solver(*p, x, yy);
+            std::copy(x.begin(), x.end(), u + b * n);
+            std::copy(yy.begin(), yy.end(), y + b * m);
+            write_stats(s, p->evaluations, stats + b * NSTATS);
+        }
+    };
+    if (nthreads <= 1) { worker(); return 0; }
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t) th.emplace_back(worker);
+    for (auto &t : th) t.join();
+    return 0;
+}
+
+} // extern "C"
