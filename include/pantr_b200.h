@@ -1,0 +1,175 @@
+/* pantr_b200 — C ABI of the B200-native batched PANTR+ALM solver.
+ *
+ * Drop-in boundary for the reference's solver call on the MPC hot path:
+ *   ALMSolver<PANTRSolver<NewtonTRDirection<DefaultConfig>>>::operator()(problem, x, y)
+ *   (alpaqa/src/alpaqa/include/alpaqa/outer/alm.hpp:157, called per MPC step from
+ *   drivers/mpc-driver.cpp:158,199,216-222), batched over B independent instances
+ *   (initial state x0, warm start u, multipliers y).  One CUDA warp-block owns one instance; the
+ *   problem functions the reference loads from CasADi-generated shared objects
+ *   (CasADiProblem.tpp:208-368) are device code inside the kernels.
+ *
+ * Plain pointers and sizes only.  All functions return 0 on success, a negative pantr_b200_error
+ * otherwise (the reference throws C++ exceptions; pantr_b200_last_error() gives the message).
+ * A handle is not thread-safe: one handle per host thread / GPU (the reference's solver and
+ * problem objects are not thread-safe either: alpaqa/python/test/test_alm_thread.py:37-62).
+ */
+#ifndef PANTR_B200_H
+#define PANTR_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum pantr_b200_error {
+    PANTR_B200_OK = 0,
+    PANTR_B200_INVALID_ARGUMENT = -1, /* std::invalid_argument in the reference */
+    PANTR_B200_CUDA_ERROR = -2,
+    PANTR_B200_NO_DEVICE = -3,        /* there is no CPU fallback */
+    PANTR_B200_OUT_OF_RANGE = -4,     /* std::out_of_range (e.g. unsupported stop criterion) */
+} pantr_b200_error;
+
+/* problem ids: the three models of python/alpaqa_mpc_benchmarks/problems */
+enum { PANTR_B200_HANGING_CHAIN = 0, PANTR_B200_QUADCOPTER = 1, PANTR_B200_REALISTIC_QUADCOPTER = 2 };
+
+/* SolverStatus, alpaqa/inner/internal/solverstatus.hpp:11-20 (same integer values) */
+enum {
+    PANTR_B200_BUSY = 0, PANTR_B200_CONVERGED, PANTR_B200_MAX_TIME, PANTR_B200_MAX_ITER,
+    PANTR_B200_NOT_FINITE, PANTR_B200_NO_PROGRESS, PANTR_B200_INTERRUPTED, PANTR_B200_EXCEPTION
+};
+/* PANOCStopCrit, alpaqa/inner/internal/panoc-stop-crit.hpp:7-102 (same integer values) */
+enum {
+    PANTR_B200_APPROX_KKT = 0, PANTR_B200_APPROX_KKT2, PANTR_B200_PROJ_GRAD_NORM,
+    PANTR_B200_PROJ_GRAD_NORM2, PANTR_B200_PROJ_GRAD_UNIT_NORM, PANTR_B200_PROJ_GRAD_UNIT_NORM2,
+    PANTR_B200_FPR_NORM, PANTR_B200_FPR_NORM2, PANTR_B200_IPOPT, PANTR_B200_LBFGSBPP
+};
+
+/* ALMParams, alpaqa/outer/alm.hpp:19-90 (wall-clock limits and printing have no device analogue) */
+typedef struct pantr_b200_alm_params {
+    double tolerance, dual_tolerance, penalty_update_factor, penalty_update_factor_lower,
+        min_penalty_update_factor, initial_penalty, initial_penalty_factor, initial_penalty_lower,
+        initial_tolerance, initial_tolerance_increase, tolerance_update_factor, rho_increase, rho_max,
+        rel_penalty_increase_threshold, max_multiplier, max_penalty, min_penalty;
+    uint32_t max_iter, max_num_initial_retries, max_num_retries, max_total_num_retries;
+    int32_t single_penalty_factor;
+} pantr_b200_alm_params;
+
+/* LipschitzEstimateParams, alpaqa/inner/internal/lipschitz.hpp:8-20 */
+typedef struct pantr_b200_lipschitz_params {
+    double L_0, epsilon, delta, Lgamma_factor;
+} pantr_b200_lipschitz_params;
+
+/* PANTRParams, alpaqa/inner/pantr.hpp:22-91 */
+typedef struct pantr_b200_pantr_params {
+    pantr_b200_lipschitz_params Lipschitz;
+    uint32_t max_iter;
+    int32_t stop_crit;
+    uint32_t max_no_progress;
+    double L_min, L_max;
+    double quadratic_upperbound_tolerance_factor, TR_tolerance_factor;
+    double ratio_threshold_acceptable, ratio_threshold_good;
+    double radius_factor_rejected, radius_factor_acceptable, radius_factor_good;
+    double initial_radius, min_radius;
+    int32_t compute_ratio_using_new_stepsize, update_direction_on_prox_step,
+        recompute_last_prox_step_after_direction_reset, disable_acceleration,
+        ratio_approx_fbe_quadratic_model;
+} pantr_b200_pantr_params;
+
+/* SteihaugCGParams, alpaqa/accelerators/steihaugcg.hpp:9-15 */
+typedef struct pantr_b200_steihaug_params {
+    double tol_scale, tol_scale_root, tol_max, max_iter_factor;
+} pantr_b200_steihaug_params;
+
+/* NewtonTRDirectionParams, alpaqa/inner/directions/pantr/newton-tr.hpp:16-23 */
+typedef struct pantr_b200_newton_tr_params {
+    int32_t rescale_on_step_size_changes;
+    double hessian_vec_factor;
+    int32_t finite_diff; /* must be 0: the exact Hessian-vector product is the device path */
+    double finite_diff_stepsize;
+} pantr_b200_newton_tr_params;
+
+/* Per-instance result: ALMSolver::Stats (alpaqa/outer/alm.hpp:104-149) with the accumulated
+ * PANTRStats (alpaqa/inner/pantr.hpp:93-110, :242-258) and the EvalCounter entries that the path
+ * touches (alpaqa/problem/problem-counters.hpp:10-58). */
+typedef struct pantr_b200_stats {
+    int32_t status;
+    uint32_t outer_iterations, inner_iterations, inner_convergence_failures;
+    uint32_t accelerated_step_rejected, direction_failures, stepsize_backtracks,
+        direction_update_rejected;
+    double eps, delta, norm_penalty, final_gamma, final_psi, final_h, final_fbe;
+    uint32_t ev_proj_multipliers, ev_prox_grad_step, ev_inactive_indices_res_lna, ev_grad_L,
+        ev_hess_psi_prod, ev_psi, ev_grad_psi, ev_psi_grad_psi, ev_f, ev_g;
+    uint32_t cg_iterations, reserved;
+    uint64_t cycles; /* SM clock cycles this instance occupied its warp */
+} pantr_b200_stats;
+
+typedef struct pantr_b200_solver pantr_b200_solver;
+
+/* Defaults = the reference struct defaults (files cited above). */
+void pantr_b200_default_params(pantr_b200_alm_params *alm, pantr_b200_pantr_params *pantr,
+                               pantr_b200_steihaug_params *cg, pantr_b200_newton_tr_params *dir);
+
+/* Replaces: solver construction in drivers/mpc-driver.cpp:47-73,104-115 + problem loading in
+ * drivers/casadi-dll-wrapper.cpp:25-67 (problem "<name>_ss2p_<horizon>").  device = CUDA ordinal. */
+int pantr_b200_create(int problem_id, int horizon, const pantr_b200_alm_params *alm,
+                      const pantr_b200_pantr_params *pantr, const pantr_b200_steihaug_params *cg,
+                      const pantr_b200_newton_tr_params *dir, int device, pantr_b200_solver **out);
+int pantr_b200_destroy(pantr_b200_solver *s);
+
+/* dims[0..4] = n, m, nx, nu, nc  (TypeErasedProblem::get_n/get_m; extra functions get_nx/nu/nc,
+ * drivers/casadi-dll-wrapper.cpp:100-126) */
+int pantr_b200_get_dims(const pantr_b200_solver *s, int64_t dims[5]);
+/* "ALMSolver<PANTRSolver<NewtonTRDirection<EigenConfigd>>>" (alpaqa/outer/alm.hpp:163-165) */
+const char *pantr_b200_get_name(const pantr_b200_solver *s);
+/* Box C of the NLP: TypeErasedProblem::get_box_C; lb, ub of length n */
+int pantr_b200_get_box_C(const pantr_b200_solver *s, double *lb, double *ub);
+/* Box D of the NLP: TypeErasedProblem::get_box_D; lb, ub of length m */
+int pantr_b200_get_box_D(const pantr_b200_solver *s, double *lb, double *ub);
+/* Initial state and initial guess of the model (extra functions get_initial_state_ptr,
+ * initial_guess; problems/problems/hanging_chain.cpp:152-165).  x0: nx, u0: n */
+int pantr_b200_get_initial(const pantr_b200_solver *s, double *x0, double *u0);
+
+/* Replaces B calls of ALMSolver::operator()(problem, x, y) (alm.tpp:19-226), HOST buffers:
+ * x0 [B*nx] in, u [B*n] in/out, y [B*m] in/out (may be NULL when m == 0), stats [B] out.
+ * Host<->device copies happen inside. */
+int pantr_b200_solve_batch(pantr_b200_solver *s, int64_t B, const double *x0, double *u, double *y,
+                           pantr_b200_stats *stats);
+/* Same with DEVICE buffers, asynchronous on `stream` (a cudaStream_t, may be NULL). */
+int pantr_b200_solve_batch_device(pantr_b200_solver *s, int64_t B, const double *d_x0, double *d_u,
+                                  double *d_y, pantr_b200_stats *d_stats, void *stream);
+
+/* Batched problem-function evaluation (TypeErasedProblem::eval_psi_grad_psi, eval_psi and
+ * eval_hess_psi_prod, type-erased-problem.hpp:31-95), HOST buffers; any output may be NULL.
+ * u [B*n], y, Sigma [B*m] (NULL if m == 0), v [B*n] or NULL -> psi [B], grad [B*n], yhat [B*m],
+ * Hv [B*n]. */
+int pantr_b200_eval_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *u,
+                          const double *y, const double *Sigma, const double *v, double *psi,
+                          double *grad, double *yhat, double *Hv);
+
+/* Plant step x+ = f_d(x, u) for B instances ("simulate_dynamics" extra function,
+ * problems/problems/formulation.hpp:258-261), HOST buffers: x [B*nx], u [B*nu] -> xn [B*nx]. */
+int pantr_b200_simulate_dynamics_batch(pantr_b200_solver *s, int64_t B, const double *x,
+                                       const double *u, double *xn);
+int pantr_b200_simulate_dynamics_batch_device(pantr_b200_solver *s, int64_t B, const double *d_x,
+                                              const double *d_u, int64_t u_stride, double *d_xn,
+                                              void *stream);
+/* Warm-start shift of drivers/mpc-driver.cpp:168-175 on DEVICE buffers: u[0:n-nu] = u[nu:n]
+ * (last block duplicated), y[0:m-nc] = y[nc:m]. */
+int pantr_b200_shift_warm_start_device(pantr_b200_solver *s, int64_t B, double *d_u, double *d_y,
+                                       void *stream);
+
+/* Optional per-iteration trace of one instance of the next solve_batch call (debug / parity):
+ * rows of 11 doubles {k, psi, fbe, gamma, eps, radius, rho, q_model, nJ, cg_iters, accepted}. */
+int pantr_b200_set_trace(pantr_b200_solver *s, int64_t instance, int max_rows);
+int pantr_b200_get_trace(pantr_b200_solver *s, double *rows, int *n_rows);
+
+/* Number of kernels this handle has launched so far. */
+int64_t pantr_b200_kernel_launches(const pantr_b200_solver *s);
+/* Resident blocks the solve kernel uses (grid size), for reporting. */
+int pantr_b200_grid_size(const pantr_b200_solver *s);
+const char *pantr_b200_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PANTR_B200_H */

@@ -1,0 +1,131 @@
+// pantr_b200: batched PANTR+ALM on B200 (sm_100a, FP64) — kernels and C ABI (include/pantr_b200.h).
+// One warp-sized thread block owns one MPC instance for the whole solve (ALM outer loop, PANTR inner
+// loop, Steihaug-CG, problem evaluations); blocks are persistent and pull instances from a queue.
+#include "pantr_device.cuh"
+#include "hanging_chain.cuh"
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace pantr;
+
+namespace {
+
+thread_local std::string g_last_error;
+int fail(int code, const std::string &msg) { g_last_error = msg; return code; }
+#define CUDA_TRY(expr)                                                                            \
+    do {                                                                                          \
+        cudaError_t e_ = (expr);                                                                  \
+        if (e_ != cudaSuccess)                                                                    \
+            return fail(PANTR_B200_CUDA_ERROR, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct KernelArgs {
+    int N, n, m, nx;
+    long long B;
+    const double *x0;
+    double *u, *y;
+    pantr_b200_stats *stats;
+    double *ws;
+    size_t ws_stride; // doubles per block
+    unsigned long long *counter;
+    Trace trace;
+};
+
+// ---- the solve kernel: ALMSolver::operator() for every instance of the batch ----
+template <class Model>
+__global__ void __launch_bounds__(32) solve_kernel(const __grid_constant__ SolverParams P,
+                                                   const __grid_constant__ KernelArgs A) {
+    __shared__ IterScalars it[3];
+    double *ws = A.ws + size_t(blockIdx.x) * A.ws_stride;
+    for (;;) {
+        unsigned long long b = 0;
+        if (lane_id() == 0) b = atomicAdd(A.counter, 1ULL);
+        b = __shfl_sync(FULL, b, 0);
+        if (b >= (unsigned long long)A.B) break;
+        long long t0 = clock64();
+        Model mdl;
+        mdl.init(A.N, A.x0 + b * A.nx, ws);
+        Pantr<Model> S(mdl, P, it, A.n, A.m, ws + Model::traj_doubles(A.N));
+        memset(&S.st, 0, sizeof(S.st));
+        S.x = A.u + b * A.n;
+        for (int i = lane_id(); i < A.m; i += 32) S.y[i] = A.y[b * A.m + i];
+        S.tracing = A.trace.rows != nullptr && (long long)b == A.trace.instance;
+        S.tr = A.trace;
+        __syncwarp();
+        S.alm_solve();
+        __syncwarp();
+        for (int i = lane_id(); i < A.m; i += 32) A.y[b * A.m + i] = S.y[i];
+        S.st.cycles = (unsigned long long)(clock64() - t0);
+        if (lane_id() == 0) A.stats[b] = S.st;
+        __syncwarp();
+    }
+}
+
+// ---- batched problem-function evaluation (eval_psi_grad_psi / eval_psi / eval_hess_psi_prod) ----
+struct EvalArgs {
+    int N, n, m, nx;
+    long long B;
+    const double *x0, *u, *y, *Sigma, *v;
+    double *psi, *grad, *yhat, *Hv;
+    double *ws;
+    size_t ws_stride;
+};
+template <class Model>
+__global__ void __launch_bounds__(32) eval_kernel(const __grid_constant__ EvalArgs A) {
+    double *ws = A.ws + size_t(blockIdx.x) * A.ws_stride;
+    for (long long b = blockIdx.x; b < A.B; b += gridDim.x) {
+        Model mdl;
+        mdl.init(A.N, A.x0 + b * A.nx, ws);
+        const double *u = A.u + b * A.n, *y = A.y ? A.y + b * A.m : nullptr,
+                     *S = A.Sigma ? A.Sigma + b * A.m : nullptr;
+        double psi = 0;
+        if (A.grad) psi = mdl.eval_psi_grad_psi(u, y, S, A.grad + b * A.n);
+        if (A.yhat || !A.grad) psi = mdl.eval_psi(u, y, S, A.yhat ? A.yhat + b * A.m : nullptr);
+        if (A.psi && lane_id() == 0) A.psi[b] = psi;
+        if (A.v && A.Hv) mdl.hess_psi_prod(u, y, S, A.v + b * A.n, A.Hv + b * A.n);
+        __syncwarp();
+    }
+}
+
+// ---- plant step: "simulate_dynamics" (problems/problems/formulation.hpp:258-261) ----
+template <class Model>
+__global__ void __launch_bounds__(32) simulate_kernel(long long B, const double *x, const double *u,
+                                                      long long u_stride, double *xn) {
+    for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+        Model mdl;
+        mdl.init(1, x + b * Model::NX, nullptr);
+        mdl.plant_step(x + b * Model::NX, u + b * u_stride, xn + b * Model::NX);
+        __syncwarp();
+    }
+}
+
+// ---- warm-start shift (drivers/mpc-driver.cpp:168-175): forward overlapping copy ----
+__global__ void __launch_bounds__(32) shift_kernel(long long B, double *u, int n, int nu, double *y, int m,
+                                                   int nc) {
+    for (long long b = blockIdx.x; b < B; b += gridDim.x) {
+        double *ub = u + b * n;
+        for (int i0 = 0; i0 < n - nu; i0 += 32) {
+            int i = i0 + lane_id();
+            double v = i < n - nu ? ub[i + nu] : 0.0;
+            __syncwarp();
+            if (i < n - nu) ub[i] = v;
+            __syncwarp();
+        }
+        if (y && m > nc) {
+            double *yb = y + b * m;
+            for (int i0 = 0; i0 < m - nc; i0 += 32) {
+                int i = i0 + lane_id();
+                double v = i < m - nc ? yb[i + nc] : 0.0;
+                __syncwarp();
+                if (i < m - nc) yb[i] = v;
+                __syncwarp();
+            }
+        }
+    }
+}
+
+} // namespace
+
+#include "pantr_b200_host.inc"

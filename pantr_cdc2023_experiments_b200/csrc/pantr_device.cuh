@@ -1,0 +1,114 @@
+// Device-side PANTR (prox-gradient + Newton trust-region / Steihaug-CG) for one instance per warp.
+// Follows, step by step, the reference's
+//   PANTRSolver::operator()        alpaqa/implementation/inner/pantr.tpp:25-473
+//   NewtonTRDirection::apply       alpaqa/inner/directions/pantr/newton-tr.hpp:91-155
+//   SteihaugCG::solve              alpaqa/accelerators/steihaugcg.hpp:39-140
+//   BoxConstrProblem::*            alpaqa/problem/box-constr-problem.hpp:59-185
+//   PANOCHelpers::*                alpaqa/implementation/inner/panoc-helpers.tpp:62-137,215-249,288-334
+// All scalars are warp-uniform; vectors are lane-strided in the instance workspace.
+#pragma once
+#include "../../include/pantr_b200.h"
+#include "warp_utils.cuh"
+
+namespace pantr {
+
+struct SolverParams {
+    pantr_b200_alm_params alm;
+    pantr_b200_pantr_params pantr;
+    pantr_b200_steihaug_params cg;
+    pantr_b200_newton_tr_params dir;
+};
+
+struct IterScalars { double psi_x, psi_xh, gamma, L, pTp, gTp, h; };
+
+struct Trace { double *rows; int *n_rows; int max_rows; long long instance; };
+
+// Number of n-vectors / m-vectors / ints in the workspace (see Workspace::bind)
+constexpr int WS_NVEC = 25, WS_MVEC = 10;
+
+template <class Model>
+struct Pantr {
+    Model &mdl;
+    const SolverParams &P;
+    IterScalars *it; // [3] in shared memory
+    int n, m;
+    // iterate storage (slot-major)
+    double *X, *XH, *G, *PP, *YH;
+    double *q, *work, *work2, *rJ, *qJ, *z, *r, *d, *Bd, *we, *wn1, *wn2, *gxh;
+    double *x, *y, *Sig, *Sig_old, *e1, *e2; // ALM-level vectors
+    int *JK;
+    pantr_b200_stats st;
+    unsigned cg_last;
+    bool tracing;
+    Trace tr;
+
+    __device__ Pantr(Model &mdl_, const SolverParams &P_, IterScalars *it_, int n_, int m_, double *ws)
+        : mdl(mdl_), P(P_), it(it_), n(n_), m(m_) {
+        double *p = ws;
+        X = p; p += 3 * n; XH = p; p += 3 * n; G = p; p += 3 * n; PP = p; p += 3 * n;
+        q = p; p += n; work = p; p += n; work2 = p; p += n; rJ = p; p += n; qJ = p; p += n;
+        z = p; p += n; r = p; p += n; d = p; p += n; Bd = p; p += n; we = p; p += n;
+        wn1 = p; p += n; wn2 = p; p += n; gxh = p; p += n; // 12 + 13 = 25 n-vectors
+        YH = p; p += 3 * m; x = nullptr;
+        y = p; p += m; Sig = p; p += m; Sig_old = p; p += m; e1 = p; p += m; e2 = p; p += m;
+        p += 2 * m; // spare (10 m-vectors)
+        JK = reinterpret_cast<int *>(p);
+    }
+    __host__ __device__ static size_t ws_doubles(int n, int m) {
+        return size_t(WS_NVEC) * n + size_t(WS_MVEC) * m + (n + 1) / 2 + 2;
+    }
+
+    // ---- problem function wrappers (+ counters, problem-with-counters.hpp:24-112) ----
+    __device__ void eval_psi_grad_psi(int s) {
+        ++st.ev_psi_grad_psi;
+        double v = mdl.eval_psi_grad_psi(X + s * n, y, Sig, G + s * n);
+        it[s].psi_x = v;
+    }
+    // box-constr-problem.hpp:59-64 ; returns h = 0
+    __device__ void prox_grad_step_raw(double gamma, const double *xx, const double *g, double *xh,
+                                       double *p) {
+        ++st.ev_prox_grad_step;
+        for (int i = lane_id(); i < n; i += 32) {
+            double xi = xx[i], s = -gamma * g[i];
+            double lo = Model::C_lb(i) - xi, hi = Model::C_ub(i) - xi;
+            double t  = s < lo ? lo : s;
+            double pi = hi < t ? hi : t;
+            p[i]  = pi;
+            xh[i] = xi + pi;
+        }
+    }
+    __device__ void eval_prox_grad_step(int s) { // pantr.tpp:88-92
+        prox_grad_step_raw(it[s].gamma, X + s * n, G + s * n, XH + s * n, PP + s * n);
+        __syncwarp();
+        double pTp = vsqnorm(PP + s * n, n), gTp = vdot(PP + s * n, G + s * n, n);
+        it[s].h = 0; it[s].pTp = pTp; it[s].gTp = gTp;
+    }
+    __device__ void eval_psi_xh(int s) { // pantr.tpp:93-95
+        ++st.ev_psi;
+        double v = mdl.eval_psi(XH + s * n, y, Sig, YH + s * m);
+        it[s].psi_xh = v;
+    }
+    __device__ double fbe(int s) const { // pantr.tpp:69
+        return it[s].psi_x + it[s].h + it[s].pTp / (2 * it[s].gamma) + it[s].gTp;
+    }
+    __device__ bool qub_violated(int s) const { // pantr.tpp:102-106
+        double margin = (1 + fabs(it[s].psi_x)) * P.pantr.quadratic_upperbound_tolerance_factor;
+        return it[s].psi_xh > it[s].psi_x + it[s].gTp + 0.5 * it[s].L * it[s].pTp + margin;
+    }
+    __device__ void backtrack_qub(int s) { // pantr.tpp:107-115
+        while (it[s].L < P.pantr.L_max && qub_violated(s)) {
+            __syncwarp();
+            double g2 = it[s].gamma / 2, L2 = it[s].L * 2;
+            __syncwarp();
+            it[s].gamma = g2; it[s].L = L2;
+            __syncwarp();
+            eval_prox_grad_step(s);
+            eval_psi_xh(s);
+            __syncwarp();
+        }
+    }
+#include "pantr_direction.cuh"
+#include "pantr_inner.cuh"
+};
+
+} // namespace pantr

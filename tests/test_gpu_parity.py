@@ -1,0 +1,71 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same inputs."""
+import numpy as np
+import pytest
+
+import oracle_util as ou
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pb():
+    import pantr_cdc2023_experiments_b200 as pb
+    return pb
+
+
+def disturbed_states(prob, B, rng, steps=5):
+    x0 = np.tile(prob.initial_state(), (B, 1))
+    for _ in range(steps):
+        x0 = prob.simulate_dynamics(x0, rng.uniform(-1, 1, (B, 3)))
+    return x0
+
+
+@pytest.mark.parametrize("N", [1, 7, 60])
+def test_hanging_chain_eval_bit_exact(pb, N):
+    prob = pb.BatchedProblem("hanging_chain", N)
+    rng = np.random.default_rng(1 + N)
+    B = 6
+    x0 = disturbed_states(prob, B, rng)
+    u = rng.uniform(-1, 1, (B, prob.n)); v = rng.standard_normal((B, prob.n))
+    psi, grad, _, Hv = prob.eval(x0, u, v=v)
+    for b in range(B):
+        po, go, _, Ho = ou.eval_(0, N, x0[b], u[b], v=v[b])
+        assert po == psi[b]
+        np.testing.assert_array_equal(go, grad[b])
+        np.testing.assert_array_equal(Ho, Hv[b])
+
+
+def test_hanging_chain_plant_step_bit_exact(pb):
+    prob = pb.BatchedProblem("hanging_chain", 5)
+    rng = np.random.default_rng(3)
+    x = disturbed_states(prob, 5, rng, steps=3)
+    u = rng.uniform(-1, 1, (5, 3))
+    xn = prob.simulate_dynamics(x, u)
+    for b in range(5):
+        np.testing.assert_array_equal(ou.simulate(0, x[b], u[b]), xn[b])
+
+
+@pytest.mark.parametrize("N,B", [(10, 8), (30, 4), (60, 3)])
+def test_hanging_chain_solve_parity(pb, N, B):
+    solver, _ = pb.make_solver(pb.benchmark_options("hanging_chain"))
+    prob = pb.BatchedProblem("hanging_chain", N)
+    rng = np.random.default_rng(100 + N)
+    x0 = disturbed_states(prob, B, rng)
+    u = np.zeros((B, prob.n))
+    solver.set_trace(prob, 0)
+    stats = solver(prob, u, None, x0=x0)
+    trace = solver.get_trace(prob)
+    par = ou.pack_params(solver)
+    for b in range(B):
+        uo, _, so, tro = ou.solve(0, N, par, x0[b], np.zeros(prob.n), trace_rows=4096 if b == 0 else 0)
+        assert int(so["status"]) == stats["status"][b] == 1
+        # north_star tolerance: iterations within +-1, iterate and objective within 1e-8 relative
+        assert abs(int(so["inner_iterations"]) - int(stats["inner_iterations"][b])) <= 1
+        np.testing.assert_allclose(u[b], uo, rtol=1e-8, atol=1e-10)
+        np.testing.assert_allclose(stats["final_psi"][b], so["final_psi"], rtol=1e-8)
+        for k in ("ev_psi", "ev_psi_grad_psi", "ev_grad_L", "ev_hess_psi_prod", "ev_prox_grad_step",
+                  "ev_grad_psi", "ev_inactive_indices_res_lna"):
+            assert abs(int(so[k]) - int(stats[k][b])) <= max(2, 0.02 * so[k]), k
+        if b == 0:  # iteration-level parity (the arithmetic is designed to be bit-identical)
+            assert len(tro) == len(trace)
+            np.testing.assert_array_equal(tro, trace)
