@@ -167,6 +167,9 @@ int pantr_b200_get_trace(pantr_b200_solver *s, double *rows, int *n_rows);
 int64_t pantr_b200_kernel_launches(const pantr_b200_solver *s);
 /* Resident blocks the solve kernel uses (grid size), for reporting. */
 int pantr_b200_grid_size(const pantr_b200_solver *s);
+/* Measured FP64 FMA throughput of the device in TFLOP/s (independent DFMA chains, best of `reps`
+ * launches): the denominator of the FP64 roofline bench.py reports. */
+int pantr_b200_measure_fp64_peak(int device, int reps, double *tflops);
 const char *pantr_b200_last_error(void);
 
 #ifdef __cplusplus

@@ -65,7 +65,8 @@ SYMBOLS = [
     "pantr_b200_solve_batch", "pantr_b200_solve_batch_device", "pantr_b200_eval_batch",
     "pantr_b200_simulate_dynamics_batch", "pantr_b200_simulate_dynamics_batch_device",
     "pantr_b200_shift_warm_start_device", "pantr_b200_set_trace", "pantr_b200_get_trace",
-    "pantr_b200_kernel_launches", "pantr_b200_grid_size", "pantr_b200_last_error",
+    "pantr_b200_kernel_launches", "pantr_b200_grid_size", "pantr_b200_measure_fp64_peak",
+    "pantr_b200_last_error",
 ]
 
 _lib = None
@@ -107,6 +108,7 @@ def load():
     lib.pantr_b200_kernel_launches.argtypes = [vp]
     lib.pantr_b200_kernel_launches.restype = i64
     lib.pantr_b200_grid_size.argtypes = [vp]
+    lib.pantr_b200_measure_fp64_peak.argtypes = [C.c_int, C.c_int, dp]
     _lib = lib
     return lib
 
