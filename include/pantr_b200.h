@@ -134,7 +134,9 @@ int pantr_b200_get_initial(const pantr_b200_solver *s, double *x0, double *u0);
  * Host<->device copies happen inside. */
 int pantr_b200_solve_batch(pantr_b200_solver *s, int64_t B, const double *x0, double *u, double *y,
                            pantr_b200_stats *stats);
-/* Same with DEVICE buffers, asynchronous on `stream` (a cudaStream_t, may be NULL). */
+/* Same with DEVICE buffers, asynchronous on `stream` (a cudaStream_t).  NULL = the handle's own
+ * non-blocking stream (note: the legacy default stream's handle is also 0; pass cudaStreamLegacy or
+ * a created stream to order the solve after other work). */
 int pantr_b200_solve_batch_device(pantr_b200_solver *s, int64_t B, const double *d_x0, double *d_u,
                                   double *d_y, pantr_b200_stats *d_stats, void *stream);
 
