@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_core.hpp header).
 // C entry points for ctypes (tests/, smoke(), bench.py cpu_baseline / --impl reference).
 #include "hanging_chain.hpp"
+#include "generic_problems.hpp"
 #include "oracle_alm.hpp"
 #include <atomic>
 #include <cstring>
@@ -147,6 +148,67 @@ int oracle_solve_batch(int problem_id, int N, const double *params, long B, cons
     for (int t = 0; t < nthreads; ++t) th.emplace_back(worker);
     for (auto &t : th) t.join();
     return 0;
+}
+
+// ---- generic problems (known-answer tests of the reference, see generic_problems.hpp) ----
+static void set_boxes(Problem &p, const double *Clb, const double *Cub, const double *Dlb, const double *Dub) {
+    if (Clb) p.C.lowerbound.assign(Clb, Clb + p.n);
+    if (Cub) p.C.upperbound.assign(Cub, Cub + p.n);
+    if (Dlb) p.D.lowerbound.assign(Dlb, Dlb + p.m);
+    if (Dub) p.D.upperbound.assign(Dub, Dub + p.m);
+}
+static int solve_generic(Problem &p, const double *params, double *x, double *y, double *stats) {
+    auto solver = make_solver(params);
+    vec xx(x, x + p.n), yy(y, y + p.m);
+    auto s = solver(p, xx, yy);
+    std::copy(xx.begin(), xx.end(), x);
+    std::copy(yy.begin(), yy.end(), y);
+    write_stats(s, p.evaluations, stats);
+    return 0;
+}
+
+// min 1/2 x'Hx + c'x + f0  s.t. x in C, Gx + g0 in D   (test-alm.cpp QPs)
+int oracle_solve_qp(long n, long m, const double *H, const double *c, double f0, const double *G,
+                    const double *g0, const double *Clb, const double *Cub, const double *Dlb,
+                    const double *Dub, const double *params, double *x, double *y, double *stats) {
+    DenseQP p(n, m);
+    std::copy(H, H + n * n, p.H.begin()); std::copy(c, c + n, p.c.begin()); p.f0 = f0;
+    if (m) { std::copy(G, G + m * n, p.G.begin()); std::copy(g0, g0 + m, p.g0.begin()); }
+    set_boxes(p, Clb, Cub, Dlb, Dub);
+    return solve_generic(p, params, x, y, stats);
+}
+
+// CasADi-generated shared object (test-casadi.cpp); composed != 0 uses the oracle's own AL formulas
+int oracle_solve_casadi(const char *so, long n, long m, const double *param, long np, const double *Clb,
+                        const double *Cub, const double *Dlb, const double *Dub, int composed,
+                        const double *params, double *x, double *y, double *stats) {
+    try {
+        if (composed) {
+            CasadiComposedProblem p(so, n, m, param, np);
+            set_boxes(p, Clb, Cub, Dlb, Dub); set_boxes(p.inner, Clb, Cub, Dlb, Dub);
+            return solve_generic(p, params, x, y, stats);
+        }
+        CasadiCProblem p(so, n, m, param, np);
+        set_boxes(p, Clb, Cub, Dlb, Dub);
+        return solve_generic(p, params, x, y, stats);
+    } catch (std::exception &) { return -2; }
+}
+
+// psi, grad psi, yhat, Hv of a CasADi-generated problem, either straight from the generated
+// psi_grad_psi / psi / hess_psi_prod (composed = 0) or through the oracle's AL compositions.
+int oracle_eval_casadi(const char *so, long n, long m, const double *param, long np, const double *Dlb,
+                       const double *Dub, int composed, const double *x, const double *y,
+                       const double *S, const double *v, double *psi, double *grad, double *yhat,
+                       double *Hv, double *psi2) {
+    try {
+        CasadiComposedProblem pc(so, n, m, param, np);
+        set_boxes(pc, nullptr, nullptr, Dlb, Dub); set_boxes(pc.inner, nullptr, nullptr, Dlb, Dub);
+        Problem &p = composed ? static_cast<Problem &>(pc) : static_cast<Problem &>(pc.inner);
+        *psi  = p.eval_psi_grad_psi(x, y, S, grad);
+        *psi2 = p.eval_psi(x, y, S, yhat);
+        if (v && Hv) p.eval_hess_psi_prod(x, y, S, 1, v, Hv);
+        return 0;
+    } catch (std::exception &) { return -2; }
 }
 
 } // extern "C"

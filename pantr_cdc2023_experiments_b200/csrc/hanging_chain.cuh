@@ -8,173 +8,383 @@
 // Lane map: l = 3*i + d, link/ball i = 0..9, dimension d = 0..2 (lanes 30,31 idle).
 //   X = position of ball i (state entry l), V = velocity of ball i (state entry 30+l, l < 27).
 //   Lanes 27..29 (the free end, whose velocity is the input) carry u[d] in the "V slot".
-// The state trajectory (N+1) x 57 and its tangent live in the instance workspace (global memory,
-// L2 resident); stage values are recomputed in the reverse sweeps (RK4 checkpointing per step).
+//
+// Per-instance model workspace (global memory, L1/L2 resident):
+//   traj  (N+1) x 57   state trajectory of the last rollout
+//   dtraj (N+1) x 57   tangent trajectory of the last Hessian-vector product
+//   iwc   N x 4 x 10   1/|dist| of every link at every RK4 stage point of the last rollout: the
+//                      adjoint and Hessian-vector sweeps rebuild the stage points from it without any
+//                      sqrt / division (same bits as recomputing: identical operations on identical
+//                      inputs), which is what keeps them FP64-add/mul bound.
+// The three sweeps are __noinline__ so that the solver contains exactly one copy of each: the
+// solve kernel's code then fits the SM instruction caches (the fully inlined version was 1.1 MB of
+// SASS and stalled 14 of 19 cycles per issue on instruction fetch: profiles/r01_v0_*).
 #pragma once
 #include "warp_utils.cuh"
 
 namespace pantr {
+namespace hc {
 
+constexpr int NX = 57, NU = 3, NL = 30, NVL = 27, NLINK = 10;
+// hanging_chain.py:9-18
+constexpr double alpha = 25, beta = 1, gamma_u = 0.01, mass = 0.03, Dspring = 0.1, Lspring = 0.033,
+                 v_max = 1, g_grav = 9.81, Ts = 0.1;
+constexpr double inv_m = 1.0 / mass, DL = Dspring * Lspring;
+constexpr double h = Ts, hh = Ts / 2, h6 = Ts / 6, h3 = 2 * (Ts / 6);
+constexpr double two_alpha = 2 * alpha, two_beta = 2 * beta, two_gamma = 2 * gamma_u;
+
+struct Lane {
+    int l, base, link;
+    bool hasV, isEnd, active;
+    double grav, ref;
+    __device__ __forceinline__ Lane() {
+        l = lane_id();
+        int d = l % 3;
+        base = l - d;
+        link = l / 3 < NLINK ? l / 3 : NLINK - 1;
+        hasV = l < NVL; active = l < NL; isEnd = active && !hasV;
+        grav = d == 2 ? -g_grav : 0.0;
+        ref  = d == 0 ? 1.0 : 0.0;
+    }
+    __device__ __forceinline__ double dot3(double p) const {
+        double a = shfl(p, base), b = shfl(p, base + 1), c = shfl(p, base + 2);
+        return (a + b) + c;
+    }
+};
+
+struct Link { double dist, c, e; };
+
+// continuous dynamics (hanging_chain.py:47-56). Vu = V for l<27, u[d] for lanes 27..29.
+// Returns iw = 1/|dist| of the lane's link.
+__device__ __forceinline__ double fc(const Lane &L, double X, double Vu, double &kX, double &kV) {
+    double Xm   = shfl(X, L.l - 3);
+    double dist = L.l >= 3 ? X - Xm : X;
+    double n2   = L.dot3(dist * dist);
+    if (!L.active) n2 = 1.0;
+    double w = sqrt(n2), iw = 1.0 / w;
+    double c  = Dspring * (1.0 - Lspring * iw);
+    double F  = dist * c;
+    double Fu = shfl(F, L.l + 3);
+    kX = Vu;
+    kV = (Fu - F) * inv_m + L.grav;
+    return iw;
+}
+// the same stage evaluation from the cached iw (no sqrt, no division)
+__device__ __forceinline__ void fc_cached(const Lane &L, double X, double Vu, double iw, double &kX,
+                                          double &kV, Link &ld, double &iw2) {
+    double Xm = shfl(X, L.l - 3);
+    ld.dist   = L.l >= 3 ? X - Xm : X;
+    ld.c      = Dspring * (1.0 - Lspring * iw);
+    iw2       = iw * iw;
+    ld.e      = (DL * iw) * iw2;
+    double F  = ld.dist * ld.c;
+    double Fu = shfl(F, L.l + 3);
+    kX = Vu;
+    kV = (Fu - F) * inv_m + L.grav;
+}
+// (dfc/d(s,u))^T w ; aVu = adjoint of V (l<27) / of u (lanes 27..29)
+__device__ __forceinline__ void vjp(const Lane &L, const Link &ld, double wX, double wV, double &aX,
+                                    double &aVu, double &Fbar, double &dotv) {
+    double wVm = shfl(wV, L.l - 3);
+    Fbar       = ((L.l >= 3 ? wVm : 0.0) - (L.hasV ? wV : 0.0)) * inv_m;
+    dotv       = L.dot3(ld.dist * Fbar);
+    double db  = ld.c * Fbar + (ld.e * dotv) * ld.dist;
+    double dbu = shfl(db, L.l + 3);
+    aX  = L.hasV ? db - dbu : db;
+    aVu = wX;
+}
+// (dfc/d(s,u)) (ds,du)
+__device__ __forceinline__ void jvp(const Lane &L, const Link &ld, double dX, double dVu, double &dkX,
+                                    double &dkV, double &ddist, double &dd) {
+    double dXm = shfl(dX, L.l - 3);
+    ddist      = L.l >= 3 ? dX - dXm : dX;
+    dd         = L.dot3(ld.dist * ddist);
+    double dF  = ld.c * ddist + (ld.e * dd) * ld.dist;
+    double dFu = shfl(dF, L.l + 3);
+    dkX = dVu;
+    dkV = (dFu - dF) * inv_m;
+}
+// second-order adjoint of one stage
+__device__ __forceinline__ void hvjp(const Lane &L, const Link &ld, double iw2, double Fbar, double dotv,
+                                     double ddist, double dd, double dwX, double dwV, double &bX,
+                                     double &bVu) {
+    double dwVm  = shfl(dwV, L.l - 3);
+    double dFbar = ((L.l >= 3 ? dwVm : 0.0) - (L.hasV ? dwV : 0.0)) * inv_m;
+    double df    = L.dot3(ddist * Fbar);
+    double dot2  = L.dot3(ld.dist * dFbar);
+    double dc    = ld.e * dd;
+    double de    = ((-3.0 * ld.e) * iw2) * dd;
+    double lin   = ld.c * dFbar + (ld.e * dot2) * ld.dist;
+    double sec   = (dc * Fbar + (de * dotv + ld.e * df) * ld.dist) + (ld.e * dotv) * ddist;
+    double ddb   = lin + sec;
+    double ddbu  = shfl(ddb, L.l + 3);
+    bX  = L.hasV ? ddb - ddbu : ddb;
+    bVu = dwX;
+}
+
+__device__ __forceinline__ void load_state(const Lane &L, const double *t, int k, double &X, double &V) {
+    const double *s = t + k * NX;
+    X = L.active ? s[L.l] : 0.0;
+    V = L.hasV ? s[NL + L.l] : 0.0;
+}
+__device__ __forceinline__ void store_state(const Lane &L, double *t, int k, double X, double V) {
+    double *s = t + k * NX;
+    if (L.active) s[L.l] = X;
+    if (L.hasV) s[NL + L.l] = V;
+}
+__device__ __forceinline__ double load_u(const Lane &L, const double *u, int k) {
+    return L.isEnd ? u[NU * k + (L.l - NVL)] : 0.0;
+}
+
+// One RK4 step (hanging_chain.py:58-66); iw_out (optional): the 4 stage values of 1/|dist|
+__device__ __forceinline__ void rk4(const Lane &L, double X, double V, double ud, double &Xn, double &Vn,
+                                    double *iw_out) {
+    double k1X, k1V, k2X, k2V, k3X, k3V, k4X, k4V;
+    const bool wr = iw_out != nullptr && L.active && L.l == L.base;
+    double iw = fc(L, X, L.hasV ? V : ud, k1X, k1V);
+    if (wr) iw_out[L.link] = iw;
+    double tX = X + hh * k1X, tV = V + hh * k1V;
+    iw = fc(L, tX, L.hasV ? tV : ud, k2X, k2V);
+    if (wr) iw_out[NLINK + L.link] = iw;
+    tX = X + hh * k2X; tV = V + hh * k2V;
+    iw = fc(L, tX, L.hasV ? tV : ud, k3X, k3V);
+    if (wr) iw_out[2 * NLINK + L.link] = iw;
+    tX = X + h * k3X; tV = V + h * k3V;
+    iw = fc(L, tX, L.hasV ? tV : ud, k4X, k4V);
+    if (wr) iw_out[3 * NLINK + L.link] = iw;
+    Xn = X + h6 * (((k1X + 2.0 * k2X) + 2.0 * k3X) + k4X);
+    Vn = V + h6 * (((k1V + 2.0 * k2V) + 2.0 * k3V) + k4V);
+}
+
+// base stage link data of one RK4 step from the cached iw (X,V = s_k ; ud = u_k on lanes 27..29)
+__device__ __forceinline__ void stages_cached(const Lane &L, double X, double V, double ud, const double *iwp,
+                                              Link (&ld)[4], double (&iw2)[4]) {
+    double Vu = L.hasV ? V : ud, kX, kV;
+    double i0 = iwp[L.link], i1 = iwp[NLINK + L.link], i2 = iwp[2 * NLINK + L.link],
+           i3 = iwp[3 * NLINK + L.link];
+    fc_cached(L, X, Vu, i0, kX, kV, ld[0], iw2[0]);
+    double tX = X + hh * kX, tV = V + hh * kV;
+    fc_cached(L, tX, L.hasV ? tV : ud, i1, kX, kV, ld[1], iw2[1]);
+    tX = X + hh * kX; tV = V + hh * kV;
+    fc_cached(L, tX, L.hasV ? tV : ud, i2, kX, kV, ld[2], iw2[2]);
+    tX = X + h * kX; tV = V + h * kV;
+    fc_cached(L, tX, L.hasV ? tV : ud, i3, kX, kV, ld[3], iw2[3]);
+}
+
+// Rollout + cost (ss.py:24-37); fills traj and iwc.  Returns f on all lanes.
+__device__ __noinline__ double rollout(int N, const double *x0, const double *u, double *traj, double *iwc) {
+    const Lane L;
+    double acc = 0, X, V;
+    X = L.active ? x0[L.l] : 0.0;
+    V = L.hasV ? x0[NL + L.l] : 0.0;
+    store_state(L, traj, 0, X, V);
+    double ud = load_u(L, u, 0);
+#pragma unroll 1
+    for (int k = 0; k < N; ++k) {
+        double un = k + 1 < N ? load_u(L, u, k + 1) : 0.0;
+        if (L.hasV) acc = acc + beta * (V * V);
+        else if (L.isEnd) { double dx = X - L.ref; acc = acc + (alpha * (dx * dx) + gamma_u * (ud * ud)); }
+        double Xn, Vn;
+        rk4(L, X, V, ud, Xn, Vn, iwc + k * (4 * NLINK));
+        X = Xn; V = Vn; ud = un;
+        store_state(L, traj, k + 1, X, V);
+    }
+    if (L.hasV) acc = acc + beta * (V * V);
+    else if (L.isEnd) { double dx = X - L.ref; acc = acc + alpha * (dx * dx); }
+    __syncwarp();
+    return warp_sum(acc);
+}
+
+// grad f by discrete adjoint; traj / iwc hold the rollout of `u`
+__device__ __noinline__ void adjoint(int N, const double *u, const double *traj, const double *iwc,
+                                     double *grad) {
+    const Lane L;
+    double X, V, lX, lV;
+    load_state(L, traj, N, X, V);
+    lX = L.isEnd ? two_alpha * (X - L.ref) : 0.0;
+    lV = L.hasV ? two_beta * V : 0.0;
+    load_state(L, traj, N - 1, X, V);
+    double ud = load_u(L, u, N - 1);
+#pragma unroll 1
+    for (int k = N - 1; k >= 0; --k) {
+        // prefetch the next (earlier) step while this one computes
+        double Xp = 0, Vp = 0, up = 0;
+        if (k > 0) { load_state(L, traj, k - 1, Xp, Vp); up = load_u(L, u, k - 1); }
+        Link ld[4]; double iw2[4];
+        stages_cached(L, X, V, ud, iwc + k * (4 * NLINK), ld, iw2);
+        double wX, wV, aX, aV, sX, sV, Fb, dt;
+        wX = h6 * lX; wV = h6 * lV;
+        vjp(L, ld[3], wX, wV, aX, aV, Fb, dt);
+        sX = lX + aX; sV = lV + aV;
+        wX = h3 * lX + h * aX; wV = h3 * lV + h * aV;
+        vjp(L, ld[2], wX, wV, aX, aV, Fb, dt);
+        sX = sX + aX; sV = sV + aV;
+        wX = h3 * lX + hh * aX; wV = h3 * lV + hh * aV;
+        vjp(L, ld[1], wX, wV, aX, aV, Fb, dt);
+        sX = sX + aX; sV = sV + aV;
+        wX = h6 * lX + hh * aX; wV = h6 * lV + hh * aV;
+        vjp(L, ld[0], wX, wV, aX, aV, Fb, dt);
+        sX = sX + aX; sV = sV + aV;
+        lX = L.isEnd ? sX + two_alpha * (X - L.ref) : sX;
+        if (L.hasV) lV = sV + two_beta * V;
+        else {
+            if (L.isEnd) grad[NU * k + (L.l - NVL)] = sV + two_gamma * ud;
+            lV = 0.0;
+        }
+        X = Xp; V = Vp; ud = up;
+    }
+}
+
+// Hv = hess f(u) v by forward-over-adjoint (the exact Hessian-vector product that
+// casadi_generator/__init__.py:181-189 defines as hess_psi_prod; with m = 0, psi = f).
+// traj / iwc hold the rollout of `u`; dtraj is scratch for the tangent trajectory.
+__device__ __noinline__ void hvp(int N, const double *u, const double *v, const double *traj, double *dtraj,
+                                 const double *iwc, double *Hv) {
+    const Lane L;
+    double X, V, dX = 0.0, dV = 0.0;
+    // ---- forward tangent sweep ----
+    store_state(L, dtraj, 0, dX, dV);
+    load_state(L, traj, 0, X, V);
+    double ud = load_u(L, u, 0), vd = load_u(L, v, 0);
+#pragma unroll 1
+    for (int k = 0; k < N; ++k) {
+        double Xp, Vp, up = 0, vp = 0;
+        load_state(L, traj, k + 1, Xp, Vp);
+        if (k + 1 < N) { up = load_u(L, u, k + 1); vp = load_u(L, v, k + 1); }
+        Link ld[4]; double iw2[4];
+        stages_cached(L, X, V, ud, iwc + k * (4 * NLINK), ld, iw2);
+        double k1X, k1V, k2X, k2V, k3X, k3V, k4X, k4V, ddist, dd;
+        jvp(L, ld[0], dX, L.hasV ? dV : vd, k1X, k1V, ddist, dd);
+        double tX = dX + hh * k1X, tV = dV + hh * k1V;
+        jvp(L, ld[1], tX, L.hasV ? tV : vd, k2X, k2V, ddist, dd);
+        tX = dX + hh * k2X; tV = dV + hh * k2V;
+        jvp(L, ld[2], tX, L.hasV ? tV : vd, k3X, k3V, ddist, dd);
+        tX = dX + h * k3X; tV = dV + h * k3V;
+        jvp(L, ld[3], tX, L.hasV ? tV : vd, k4X, k4V, ddist, dd);
+        dX = dX + h6 * (((k1X + 2.0 * k2X) + 2.0 * k3X) + k4X);
+        dV = dV + h6 * (((k1V + 2.0 * k2V) + 2.0 * k3V) + k4V);
+        store_state(L, dtraj, k + 1, dX, dV);
+        X = Xp; V = Vp; ud = up; vd = vp;
+    }
+    __syncwarp();
+    // ---- reverse sweep for lambda and mu = d lambda ----  (X, V = s_N here)
+    double lX, lV, mX, mV;
+    lX = L.isEnd ? two_alpha * (X - L.ref) : 0.0;
+    mX = L.isEnd ? two_alpha * dX : 0.0;
+    lV = L.hasV ? two_beta * V : 0.0;
+    mV = L.hasV ? two_beta * dV : 0.0;
+    load_state(L, traj, N - 1, X, V);
+    load_state(L, dtraj, N - 1, dX, dV);
+    ud = load_u(L, u, N - 1); vd = load_u(L, v, N - 1);
+#pragma unroll 1
+    for (int k = N - 1; k >= 0; --k) {
+        double Xp = 0, Vp = 0, dXp = 0, dVp = 0, up = 0, vp = 0;
+        if (k > 0) {
+            load_state(L, traj, k - 1, Xp, Vp); load_state(L, dtraj, k - 1, dXp, dVp);
+            up = load_u(L, u, k - 1); vp = load_u(L, v, k - 1);
+        }
+        Link ld[4]; double iw2[4];
+        stages_cached(L, X, V, ud, iwc + k * (4 * NLINK), ld, iw2);
+        double ddist[4], dd[4];
+        {
+            double kX, kV;
+            jvp(L, ld[0], dX, L.hasV ? dV : vd, kX, kV, ddist[0], dd[0]);
+            double tX = dX + hh * kX, tV = dV + hh * kV;
+            jvp(L, ld[1], tX, L.hasV ? tV : vd, kX, kV, ddist[1], dd[1]);
+            tX = dX + hh * kX; tV = dV + hh * kV;
+            jvp(L, ld[2], tX, L.hasV ? tV : vd, kX, kV, ddist[2], dd[2]);
+            tX = dX + h * kX; tV = dV + h * kV;
+            jvp(L, ld[3], tX, L.hasV ? tV : vd, kX, kV, ddist[3], dd[3]);
+        }
+        double wX, wV, aX, aV, sX, sV, dwX, dwV, bX, bV, tX, tV, Fb, dt;
+        // stage 4
+        wX = h6 * lX; wV = h6 * lV; dwX = h6 * mX; dwV = h6 * mV;
+        vjp(L, ld[3], wX, wV, aX, aV, Fb, dt);
+        hvjp(L, ld[3], iw2[3], Fb, dt, ddist[3], dd[3], dwX, dwV, bX, bV);
+        sX = lX + aX; sV = lV + aV; tX = mX + bX; tV = mV + bV;
+        // stage 3
+        wX = h3 * lX + h * aX; wV = h3 * lV + h * aV; dwX = h3 * mX + h * bX; dwV = h3 * mV + h * bV;
+        vjp(L, ld[2], wX, wV, aX, aV, Fb, dt);
+        hvjp(L, ld[2], iw2[2], Fb, dt, ddist[2], dd[2], dwX, dwV, bX, bV);
+        sX = sX + aX; sV = sV + aV; tX = tX + bX; tV = tV + bV;
+        // stage 2
+        wX = h3 * lX + hh * aX; wV = h3 * lV + hh * aV; dwX = h3 * mX + hh * bX; dwV = h3 * mV + hh * bV;
+        vjp(L, ld[1], wX, wV, aX, aV, Fb, dt);
+        hvjp(L, ld[1], iw2[1], Fb, dt, ddist[1], dd[1], dwX, dwV, bX, bV);
+        sX = sX + aX; sV = sV + aV; tX = tX + bX; tV = tV + bV;
+        // stage 1
+        wX = h6 * lX + hh * aX; wV = h6 * lV + hh * aV; dwX = h6 * mX + hh * bX; dwV = h6 * mV + hh * bV;
+        vjp(L, ld[0], wX, wV, aX, aV, Fb, dt);
+        hvjp(L, ld[0], iw2[0], Fb, dt, ddist[0], dd[0], dwX, dwV, bX, bV);
+        sX = sX + aX; sV = sV + aV; tX = tX + bX; tV = tV + bV;
+        // stage cost
+        lX = L.isEnd ? sX + two_alpha * (X - L.ref) : sX;
+        mX = L.isEnd ? tX + two_alpha * dX : tX;
+        if (L.hasV) { lV = sV + two_beta * V; mV = tV + two_beta * dV; }
+        else {
+            if (L.isEnd) Hv[NU * k + (L.l - NVL)] = tV + two_gamma * vd;
+            lV = 0.0; mV = 0.0;
+        }
+        X = Xp; V = Vp; dX = dXp; dV = dVp; ud = up; vd = vp;
+    }
+}
+
+} // namespace hc
+
+// Problem-function surface the solver sees (what CasADiProblem::eval_* would compute, m = 0).
 struct HangingChain {
-    static constexpr int NX = 57, NU = 3, NL = 30, NVL = 27, NC = 0;
-    static constexpr double alpha = 25, beta = 1, gamma_u = 0.01, mass = 0.03, Dspring = 0.1,
-                            Lspring = 0.033, v_max = 1, g_grav = 9.81, Ts = 0.1;
+    static constexpr int NX = hc::NX, NU = hc::NU, NC = 0;
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int) { return 0; }
-    __host__ __device__ static int traj_doubles(int N) { return 2 * (N + 1) * NX; }
-    __host__ __device__ static double C_lb(int) { return -v_max; }
-    __host__ __device__ static double C_ub(int) { return +v_max; }
+    // traj + dtraj + iwc
+    __host__ __device__ static int traj_doubles(int N) { return 2 * (N + 1) * NX + 4 * hc::NLINK * N; }
+    __host__ __device__ static double C_lb(int) { return -hc::v_max; } // hanging_chain.py:82-84
+    __host__ __device__ static double C_ub(int) { return +hc::v_max; }
     __host__ __device__ static double D_lb(int, int) { return 0; }
     __host__ __device__ static double D_ub(int, int) { return 0; }
-    __device__ void eval_f_g_sqnorm(const double *u, double &f, double &g2) { f = rollout(u); g2 = 0; }
     static void initial_state(double *x) { // hanging_chain.py:92-96
         for (int i = 0; i < NX; ++i) x[i] = 0;
         for (int i = 0; i < 10; ++i) x[3 * i] = double(i + 1) / 10;
     }
     static void initial_guess(double *u, int N) { for (int i = 0; i < NU * N; ++i) u[i] = 0; }
 
-    struct Link { double dist, c, e, iw2; };
-
-    // per-lane constants
-    int l, d, base;
-    bool hasV, isEnd, active;
-    double grav, ref;
-    double inv_m, DL, h, hh, h6, h3, two_alpha, two_beta, two_gamma;
     int N;
     const double *x0;
-    double *traj, *dtraj;
+    double *traj, *dtraj, *iwc;
 
-    __device__ void init(int N_, const double *x0_, double *ws_traj) {
-        l = lane_id(); d = l % 3; base = l - d;
-        hasV = l < NVL; active = l < NL; isEnd = active && !hasV;
-        grav = d == 2 ? -g_grav : 0.0; ref = d == 0 ? 1.0 : 0.0;
-        inv_m = 1.0 / mass; DL = Dspring * Lspring;
-        h = Ts; hh = Ts / 2; h6 = Ts / 6; h3 = 2 * (Ts / 6);
-        two_alpha = 2 * alpha; two_beta = 2 * beta; two_gamma = 2 * gamma_u;
-        N = N_; x0 = x0_; traj = ws_traj; dtraj = ws_traj + (N_ + 1) * NX;
+    __device__ void init(int N_, const double *x0_, double *ws) {
+        N = N_; x0 = x0_; traj = ws; dtraj = ws + (N_ + 1) * NX; iwc = ws + 2 * (N_ + 1) * NX;
     }
-
-    __device__ __forceinline__ double dot3(double p) const {
-        double a = shfl(p, base), b = shfl(p, base + 1), c = shfl(p, base + 2);
-        return (a + b) + c;
+    __device__ void eval_f_g_sqnorm(const double *u, double &f, double &g2) { f = eval_psi(u, nullptr, nullptr, nullptr); g2 = 0; }
+    __device__ double eval_psi(const double *x, const double *, const double *, double *) {
+        __syncwarp();
+        double f = hc::rollout(N, x0, x, traj, iwc);
+        __syncwarp();
+        return f;
     }
-    // continuous dynamics (hanging_chain.py:47-56). Vu = V for l<27, u[d] for lanes 27..29.
-    __device__ __forceinline__ void fc(double X, double Vu, double &kX, double &kV, Link &ld) const {
-        double Xm = shfl(X, l - 3);
-        ld.dist   = l >= 3 ? X - Xm : X;
-        double sq = ld.dist * ld.dist;
-        double n2 = dot3(sq);
-        if (!active) n2 = 1.0;
-        double w = sqrt(n2), iw = 1.0 / w;
-        ld.c   = Dspring * (1.0 - Lspring * iw);
-        ld.iw2 = iw * iw;
-        ld.e   = (DL * iw) * ld.iw2;
-        double F  = ld.dist * ld.c;
-        double Fu = shfl(F, l + 3);
-        kX = Vu;
-        kV = (Fu - F) * inv_m + grav;
+    __device__ double eval_psi_grad_psi(const double *x, const double *, const double *, double *grad) {
+        __syncwarp();
+        double f = hc::rollout(N, x0, x, traj, iwc);
+        __syncwarp();
+        hc::adjoint(N, x, traj, iwc, grad);
+        __syncwarp();
+        return f;
     }
-    // (dfc/d(s,u))^T w ; aVu = adjoint of V (l<27) / of u (lanes 27..29)
-    __device__ __forceinline__ void vjp(const Link &ld, double wX, double wV, double &aX, double &aVu,
-                                        double &Fbar, double &dotv) const {
-        double wVm = shfl(wV, l - 3);
-        Fbar       = ((l >= 3 ? wVm : 0.0) - (hasV ? wV : 0.0)) * inv_m;
-        dotv       = dot3(ld.dist * Fbar);
-        double db  = ld.c * Fbar + (ld.e * dotv) * ld.dist;
-        double dbu = shfl(db, l + 3);
-        aX  = hasV ? db - dbu : db;
-        aVu = wX;
+    /// Requires that the last rollout was at x (PANTR guarantees this: pantr.tpp:314 then :373).
+    __device__ void hess_psi_prod(const double *x, const double *, const double *, const double *v, double *Hv) {
+        __syncwarp();
+        hc::hvp(N, x, v, traj, dtraj, iwc, Hv);
+        __syncwarp();
     }
-    // (dfc/d(s,u)) (ds,du)
-    __device__ __forceinline__ void jvp(const Link &ld, double dX, double dVu, double &dkX, double &dkV,
-                                        double &ddist, double &dd) const {
-        double dXm = shfl(dX, l - 3);
-        ddist      = l >= 3 ? dX - dXm : dX;
-        dd         = dot3(ld.dist * ddist);
-        double dF  = ld.c * ddist + (ld.e * dd) * ld.dist;
-        double dFu = shfl(dF, l + 3);
-        dkX = dVu;
-        dkV = (dFu - dF) * inv_m;
+    /// Plant step x+ = f_d(x, u) (problems/problems/formulation.hpp:258-261)
+    __device__ static void plant_step(const double *x, const double *u, double *xn) {
+        const hc::Lane L;
+        double X = L.active ? x[L.l] : 0.0, V = L.hasV ? x[hc::NL + L.l] : 0.0, ud = L.isEnd ? u[L.l - hc::NVL] : 0.0;
+        double Xn, Vn;
+        hc::rk4(L, X, V, ud, Xn, Vn, nullptr);
+        if (L.active) xn[L.l] = Xn;
+        if (L.hasV) xn[hc::NL + L.l] = Vn;
     }
-    // second-order adjoint of one stage
-    __device__ __forceinline__ void hvjp(const Link &ld, double Fbar, double dotv, double ddist, double dd,
-                                         double dwX, double dwV, double &bX, double &bVu) const {
-        double dwVm  = shfl(dwV, l - 3);
-        double dFbar = ((l >= 3 ? dwVm : 0.0) - (hasV ? dwV : 0.0)) * inv_m;
-        double df    = dot3(ddist * Fbar);
-        double dot2  = dot3(ld.dist * dFbar);
-        double dc    = ld.e * dd;
-        double de    = ((-3.0 * ld.e) * ld.iw2) * dd;
-        double lin   = ld.c * dFbar + (ld.e * dot2) * ld.dist;
-        double sec   = (dc * Fbar + (de * dotv + ld.e * df) * ld.dist) + (ld.e * dotv) * ddist;
-        double ddb   = lin + sec;
-        double ddbu  = shfl(ddb, l + 3);
-        bX  = hasV ? ddb - ddbu : ddb;
-        bVu = dwX;
-    }
-
-    __device__ __forceinline__ void load_state(const double *t, int k, double &X, double &V) const {
-        const double *s = t + k * NX;
-        X = active ? s[l] : 0.0;
-        V = hasV ? s[NL + l] : 0.0;
-    }
-    __device__ __forceinline__ void store_state(double *t, int k, double X, double V) const {
-        double *s = t + k * NX;
-        if (active) s[l] = X;
-        if (hasV) s[NL + l] = V;
-    }
-    __device__ __forceinline__ double load_u(const double *u, int k) const {
-        return isEnd ? u[NU * k + (l - NVL)] : 0.0;
-    }
-
-    // base stage link data of one RK4 step (X,V = s_k ; ud = u_k on lanes 27..29)
-    __device__ __forceinline__ void stages(double X, double V, double ud, Link (&ld)[4]) const {
-        double Vu = hasV ? V : ud, kX, kV;
-        fc(X, Vu, kX, kV, ld[0]);
-        double tX = X + hh * kX, tV = V + hh * kV;
-        fc(tX, hasV ? tV : ud, kX, kV, ld[1]);
-        tX = X + hh * kX; tV = V + hh * kV;
-        fc(tX, hasV ? tV : ud, kX, kV, ld[2]);
-        tX = X + h * kX; tV = V + h * kV;
-        fc(tX, hasV ? tV : ud, kX, kV, ld[3]);
-    }
-
-    // One RK4 step (hanging_chain.py:58-66)
-    __device__ __forceinline__ void rk4(double X, double V, double ud, double &Xn, double &Vn) const {
-        Link ld;
-        double k1X, k1V, k2X, k2V, k3X, k3V, k4X, k4V;
-        fc(X, hasV ? V : ud, k1X, k1V, ld);
-        double tX = X + hh * k1X, tV = V + hh * k1V;
-        fc(tX, hasV ? tV : ud, k2X, k2V, ld);
-        tX = X + hh * k2X; tV = V + hh * k2V;
-        fc(tX, hasV ? tV : ud, k3X, k3V, ld);
-        tX = X + h * k3X; tV = V + h * k3V;
-        fc(tX, hasV ? tV : ud, k4X, k4V, ld);
-        Xn = X + h6 * (((k1X + 2.0 * k2X) + 2.0 * k3X) + k4X);
-        Vn = V + h6 * (((k1V + 2.0 * k2V) + 2.0 * k3V) + k4V);
-    }
-
-    // Rollout + cost (ss.py:24-37); fills traj.  Returns f on all lanes.
-    __device__ double rollout(const double *u) {
-        double acc = 0, X, V;
-        X = active ? x0[l] : 0.0;
-        V = hasV ? x0[NL + l] : 0.0;
-        store_state(traj, 0, X, V);
-        double ud = load_u(u, 0);
-        for (int k = 0; k < N; ++k) {
-            double un = k + 1 < N ? load_u(u, k + 1) : 0.0;
-            if (hasV) acc = acc + beta * (V * V);
-            else if (isEnd) { double dx = X - ref; acc = acc + (alpha * (dx * dx) + gamma_u * (ud * ud)); }
-            double Xn, Vn;
-            rk4(X, V, ud, Xn, Vn);
-            X = Xn; V = Vn; ud = un;
-            store_state(traj, k + 1, X, V);
-        }
-        if (hasV) acc = acc + beta * (V * V);
-        else if (isEnd) { double dx = X - ref; acc = acc + alpha * (dx * dx); }
-        return warp_sum(acc);
-    }
-#include "hanging_chain_sweeps.cuh"
 };
 
 } // namespace pantr

@@ -35,7 +35,7 @@ struct KernelArgs {
 
 // ---- the solve kernel: ALMSolver::operator() for every instance of the batch ----
 template <class Model>
-__global__ void __launch_bounds__(32) solve_kernel(const __grid_constant__ SolverParams P,
+__global__ void __launch_bounds__(32, 16) solve_kernel(const __grid_constant__ SolverParams P,
                                                    const __grid_constant__ KernelArgs A) {
     __shared__ IterScalars it[3];
     double *ws = A.ws + size_t(blockIdx.x) * A.ws_stride;
