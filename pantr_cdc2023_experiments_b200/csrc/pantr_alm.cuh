@@ -48,7 +48,7 @@
     __device__ void alm_solve() {
         const auto &a = P.alm;
         st.status = PANTR_B200_BUSY;
-        if (m == 0) { // alm.tpp:29-52
+        if (Model::NC == 0) { // alm.tpp:29-52 (m == 0  <=>  the model has no general constraints)
             InnerResult ps = inner_solve(a.tolerance, true, nullptr);
             accumulate(ps);
             st.eps = ps.eps; st.delta = 0; st.norm_penalty = 0; st.outer_iterations = 1;

@@ -59,13 +59,13 @@ struct Pantr {
     }
 
     // ---- problem function wrappers (+ counters, problem-with-counters.hpp:24-112) ----
-    __device__ void eval_psi_grad_psi(int s) {
+    __device__ __noinline__ void eval_psi_grad_psi(int s) {
         ++st.ev_psi_grad_psi;
         double v = mdl.eval_psi_grad_psi(X + s * n, y, Sig, G + s * n);
         it[s].psi_x = v;
     }
     // box-constr-problem.hpp:59-64 ; returns h = 0
-    __device__ void prox_grad_step_raw(double gamma, const double *xx, const double *g, double *xh,
+    __device__ __noinline__ void prox_grad_step_raw(double gamma, const double *xx, const double *g, double *xh,
                                        double *p) {
         ++st.ev_prox_grad_step;
         for (int i = lane_id(); i < n; i += 32) {
@@ -77,13 +77,13 @@ struct Pantr {
             xh[i] = xi + pi;
         }
     }
-    __device__ void eval_prox_grad_step(int s) { // pantr.tpp:88-92
+    __device__ __noinline__ void eval_prox_grad_step(int s) { // pantr.tpp:88-92
         prox_grad_step_raw(it[s].gamma, X + s * n, G + s * n, XH + s * n, PP + s * n);
         __syncwarp();
         double pTp = vsqnorm(PP + s * n, n), gTp = vdot(PP + s * n, G + s * n, n);
         it[s].h = 0; it[s].pTp = pTp; it[s].gTp = gTp;
     }
-    __device__ void eval_psi_xh(int s) { // pantr.tpp:93-95
+    __device__ __noinline__ void eval_psi_xh(int s) { // pantr.tpp:93-95
         ++st.ev_psi;
         double v = mdl.eval_psi(XH + s * n, y, Sig, YH + s * m);
         it[s].psi_xh = v;
@@ -95,7 +95,7 @@ struct Pantr {
         double margin = (1 + fabs(it[s].psi_x)) * P.pantr.quadratic_upperbound_tolerance_factor;
         return it[s].psi_xh > it[s].psi_x + it[s].gTp + 0.5 * it[s].L * it[s].pTp + margin;
     }
-    __device__ void backtrack_qub(int s) { // pantr.tpp:107-115
+    __device__ __noinline__ void backtrack_qub(int s) { // pantr.tpp:107-115
         while (it[s].L < P.pantr.L_max && qub_violated(s)) {
             __syncwarp();
             double g2 = it[s].gamma / 2, L2 = it[s].L * 2;

@@ -4,7 +4,7 @@
     // eval_inactive_indices_res_lna (box-constr-problem.hpp:151-185) + IndexSet::compute_complement
     // (util/index-set.hpp:46-50): ascending J in JK[0..nJ), ascending K in JK[nJ..n), by
     // ballot / prefix-popcount compaction.
-    __device__ int inactive_indices(double gamma, const double *xx, const double *g) {
+    __device__ __noinline__ int inactive_indices(double gamma, const double *xx, const double *g) {
         ++st.ev_inactive_indices_res_lna;
         const int lane = lane_id();
         const unsigned lt = (1u << lane) - 1u;
@@ -37,7 +37,7 @@
     }
 
     // hess_vec_mult of newton-tr.hpp:134-149: Bp = (H work)(J), work(J) = p, zero elsewhere
-    __device__ void hess_vec_mult(const double *xx, const double *p, double *Bp, int nJ) {
+    __device__ __noinline__ void hess_vec_mult(const double *xx, const double *p, double *Bp, int nJ) {
         const int *J = JK;
         for (int i = lane_id(); i < n; i += 32) work[i] = 0.0;
         __syncwarp();
@@ -48,12 +48,12 @@
         __syncwarp();
     }
     // eval lambda of steihaugcg.hpp:62-65
-    __device__ double cg_eval(const double *xx, const double *p, const double *g, int nJ) {
+    __device__ __noinline__ double cg_eval(const double *xx, const double *p, const double *g, int nJ) {
         hess_vec_mult(xx, p, we, nJ);
         return vdot(p, g, nJ) + 0.5 * vdot(p, we, nJ);
     }
     // steihaugcg.hpp:122-140
-    __device__ void boundaries(const double *zz, const double *dd_, int nJ, double radius, double &lo,
+    __device__ __noinline__ void boundaries(const double *zz, const double *dd_, int nJ, double radius, double &lo,
                                double &hi) {
         double a = vsqnorm(dd_, nJ);
         double b = 2 * vdot(zz, dd_, nJ);
@@ -65,7 +65,7 @@
         lo = fmin(ta, tb); hi = fmax(ta, tb);
     }
     // steihaugcg.hpp:39-117 ; g = rJ, step -> s (both compressed, length nJ)
-    __device__ double steihaug(const double *xx, const double *g, int nJ, double radius, double *s) {
+    __device__ __noinline__ double steihaug(const double *xx, const double *g, int nJ, double radius, double *s) {
         const int lane = lane_id();
         for (int j = lane; j < nJ; j += 32) { double gj = g[j]; z[j] = 0.0; r[j] = gj; d[j] = -gj; }
         __syncwarp();
@@ -117,7 +117,7 @@
     }
 
     // newton-tr.hpp:91-155 (exact Hessian branch). xx, pk, g: prox iterate. Returns q_model.
-    __device__ double direction_apply(double gamma, const double *xx, const double *pk, const double *g,
+    __device__ __noinline__ double direction_apply(double gamma, const double *xx, const double *pk, const double *g,
                                       double radius, double *qk, int &nJ_out) {
         const int lane = lane_id();
         const int nJ = inactive_indices(gamma, xx, g), nK = n - nJ;

@@ -4,7 +4,7 @@
     struct InnerResult { int status; double eps; unsigned iterations; };
 
     // panoc-helpers.tpp:62-137 (criteria that do not need grad psi(x_hat))
-    __device__ double calc_error_stop_crit(int c) {
+    __device__ __noinline__ double calc_error_stop_crit(int c) {
         const int crit = P.pantr.stop_crit;
         const double *pk = PP + c * n;
         switch (crit) {
@@ -25,7 +25,7 @@
     }
 
     // x (in/out) lives in this->x ; y in this->y ; Sigma in this->Sig ; err_z -> errz (may be null)
-    __device__ InnerResult inner_solve(double tolerance_opt, bool always_overwrite, double *errz) {
+    __device__ __noinline__ InnerResult inner_solve(double tolerance_opt, bool always_overwrite, double *errz) {
         const auto &pp = P.pantr;
         int curr = 0, prox = 1, cand = 2;
         InnerResult res{PANTR_B200_BUSY, INFINITY, 0};
