@@ -157,11 +157,15 @@ __device__ __forceinline__ void rk4(const Lane &L, double X, double V, double ud
 }
 
 // base stage link data of one RK4 step from the cached iw (X,V = s_k ; ud = u_k on lanes 27..29)
-__device__ __forceinline__ void stages_cached(const Lane &L, double X, double V, double ud, const double *iwp,
+struct IW { double i0, i1, i2, i3; };
+__device__ __forceinline__ IW load_iw(const Lane &L, const double *iwc, int k) {
+    const double *p = iwc + k * (4 * NLINK) + L.link;
+    return IW{p[0], p[NLINK], p[2 * NLINK], p[3 * NLINK]};
+}
+__device__ __forceinline__ void stages_cached(const Lane &L, double X, double V, double ud, const IW &iw,
                                               Link (&ld)[4], double (&iw2)[4]) {
     double Vu = L.hasV ? V : ud, kX, kV;
-    double i0 = iwp[L.link], i1 = iwp[NLINK + L.link], i2 = iwp[2 * NLINK + L.link],
-           i3 = iwp[3 * NLINK + L.link];
+    const double i0 = iw.i0, i1 = iw.i1, i2 = iw.i2, i3 = iw.i3;
     fc_cached(L, X, Vu, i0, kX, kV, ld[0], iw2[0]);
     double tX = X + hh * kX, tV = V + hh * kV;
     fc_cached(L, tX, L.hasV ? tV : ud, i1, kX, kV, ld[1], iw2[1]);
@@ -173,6 +177,8 @@ __device__ __forceinline__ void stages_cached(const Lane &L, double X, double V,
 
 // Rollout + cost (ss.py:24-37); fills traj and iwc.  Returns f on all lanes.
 __device__ __noinline__ double rollout(int N, const double *x0, const double *u, double *traj, double *iwc) {
+    __builtin_assume(__isGlobal(x0)); __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(traj));
+    __builtin_assume(__isGlobal(iwc));
     const Lane L;
     double acc = 0, X, V;
     X = L.active ? x0[L.l] : 0.0;
@@ -198,6 +204,8 @@ __device__ __noinline__ double rollout(int N, const double *x0, const double *u,
 // grad f by discrete adjoint; traj / iwc hold the rollout of `u`
 __device__ __noinline__ void adjoint(int N, const double *u, const double *traj, const double *iwc,
                                      double *grad) {
+    __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(traj)); __builtin_assume(__isGlobal(iwc));
+    __builtin_assume(__isGlobal(grad));
     const Lane L;
     double X, V, lX, lV;
     load_state(L, traj, N, X, V);
@@ -205,13 +213,15 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
     lV = L.hasV ? two_beta * V : 0.0;
     load_state(L, traj, N - 1, X, V);
     double ud = load_u(L, u, N - 1);
+    IW iw = load_iw(L, iwc, N - 1);
 #pragma unroll 1
     for (int k = N - 1; k >= 0; --k) {
         // prefetch the next (earlier) step while this one computes
         double Xp = 0, Vp = 0, up = 0;
-        if (k > 0) { load_state(L, traj, k - 1, Xp, Vp); up = load_u(L, u, k - 1); }
+        IW iwp = iw;
+        if (k > 0) { load_state(L, traj, k - 1, Xp, Vp); up = load_u(L, u, k - 1); iwp = load_iw(L, iwc, k - 1); }
         Link ld[4]; double iw2[4];
-        stages_cached(L, X, V, ud, iwc + k * (4 * NLINK), ld, iw2);
+        stages_cached(L, X, V, ud, iw, ld, iw2);
         double wX, wV, aX, aV, sX, sV, Fb, dt;
         wX = h6 * lX; wV = h6 * lV;
         vjp(L, ld[3], wX, wV, aX, aV, Fb, dt);
@@ -231,7 +241,7 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
             if (L.isEnd) grad[NU * k + (L.l - NVL)] = sV + two_gamma * ud;
             lV = 0.0;
         }
-        X = Xp; V = Vp; ud = up;
+        X = Xp; V = Vp; ud = up; iw = iwp;
     }
 }
 
@@ -240,19 +250,23 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
 // traj / iwc hold the rollout of `u`; dtraj is scratch for the tangent trajectory.
 __device__ __noinline__ void hvp(int N, const double *u, const double *v, const double *traj, double *dtraj,
                                  const double *iwc, double *Hv) {
+    __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(v)); __builtin_assume(__isGlobal(traj));
+    __builtin_assume(__isGlobal(dtraj)); __builtin_assume(__isGlobal(iwc)); __builtin_assume(__isGlobal(Hv));
     const Lane L;
     double X, V, dX = 0.0, dV = 0.0;
     // ---- forward tangent sweep ----
     store_state(L, dtraj, 0, dX, dV);
     load_state(L, traj, 0, X, V);
     double ud = load_u(L, u, 0), vd = load_u(L, v, 0);
+    IW iw = load_iw(L, iwc, 0);
 #pragma unroll 1
     for (int k = 0; k < N; ++k) {
         double Xp, Vp, up = 0, vp = 0;
+        IW iwp = iw;
         load_state(L, traj, k + 1, Xp, Vp);
-        if (k + 1 < N) { up = load_u(L, u, k + 1); vp = load_u(L, v, k + 1); }
+        if (k + 1 < N) { up = load_u(L, u, k + 1); vp = load_u(L, v, k + 1); iwp = load_iw(L, iwc, k + 1); }
         Link ld[4]; double iw2[4];
-        stages_cached(L, X, V, ud, iwc + k * (4 * NLINK), ld, iw2);
+        stages_cached(L, X, V, ud, iw, ld, iw2);
         double k1X, k1V, k2X, k2V, k3X, k3V, k4X, k4V, ddist, dd;
         jvp(L, ld[0], dX, L.hasV ? dV : vd, k1X, k1V, ddist, dd);
         double tX = dX + hh * k1X, tV = dV + hh * k1V;
@@ -264,7 +278,7 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
         dX = dX + h6 * (((k1X + 2.0 * k2X) + 2.0 * k3X) + k4X);
         dV = dV + h6 * (((k1V + 2.0 * k2V) + 2.0 * k3V) + k4V);
         store_state(L, dtraj, k + 1, dX, dV);
-        X = Xp; V = Vp; ud = up; vd = vp;
+        X = Xp; V = Vp; ud = up; vd = vp; iw = iwp;
     }
     __syncwarp();
     // ---- reverse sweep for lambda and mu = d lambda ----  (X, V = s_N here)
@@ -276,15 +290,17 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
     load_state(L, traj, N - 1, X, V);
     load_state(L, dtraj, N - 1, dX, dV);
     ud = load_u(L, u, N - 1); vd = load_u(L, v, N - 1);
+    iw = load_iw(L, iwc, N - 1);
 #pragma unroll 1
     for (int k = N - 1; k >= 0; --k) {
         double Xp = 0, Vp = 0, dXp = 0, dVp = 0, up = 0, vp = 0;
+        IW iwp = iw;
         if (k > 0) {
             load_state(L, traj, k - 1, Xp, Vp); load_state(L, dtraj, k - 1, dXp, dVp);
-            up = load_u(L, u, k - 1); vp = load_u(L, v, k - 1);
+            up = load_u(L, u, k - 1); vp = load_u(L, v, k - 1); iwp = load_iw(L, iwc, k - 1);
         }
         Link ld[4]; double iw2[4];
-        stages_cached(L, X, V, ud, iwc + k * (4 * NLINK), ld, iw2);
+        stages_cached(L, X, V, ud, iw, ld, iw2);
         double ddist[4], dd[4];
         {
             double kX, kV;
@@ -325,7 +341,7 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
             if (L.isEnd) Hv[NU * k + (L.l - NVL)] = tV + two_gamma * vd;
             lV = 0.0; mV = 0.0;
         }
-        X = Xp; V = Vp; dX = dXp; dV = dVp; ud = up; vd = vp;
+        X = Xp; V = Vp; dX = dXp; dV = dVp; ud = up; vd = vp; iw = iwp;
     }
 }
 

@@ -11,7 +11,12 @@ namespace pantr {
 constexpr unsigned FULL = 0xffffffffu;
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
-__device__ __forceinline__ double shfl(double v, int src) { return __shfl_sync(FULL, v, src); }
+__device__ __forceinline__ double shfl(double v, int src) {
+    int lo = __double2loint(v), hi = __double2hiint(v);
+    lo = __shfl_sync(FULL, lo, src);
+    hi = __shfl_sync(FULL, hi, src);
+    return __hiloint2double(hi, lo);
+}
 
 __device__ __forceinline__ double warp_sum(double p) {
 #pragma unroll
