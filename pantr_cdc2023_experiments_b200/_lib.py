@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpantr_b200.so")
+LIB_PATH = os.environ.get("PANTR_B200_LIB", os.path.join(_HERE, "libpantr_b200.so"))  # override: experiments only
 
 
 class ALMParamsC(C.Structure):

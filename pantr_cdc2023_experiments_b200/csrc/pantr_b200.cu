@@ -8,6 +8,9 @@
 #include <string>
 #include <vector>
 
+#ifndef PANTR_MIN_BLOCKS
+#define PANTR_MIN_BLOCKS 16 // resident warps per SM the solve kernel is compiled for (128 registers)
+#endif
 using namespace pantr;
 
 namespace {
@@ -35,7 +38,7 @@ struct KernelArgs {
 
 // ---- the solve kernel: ALMSolver::operator() for every instance of the batch ----
 template <class Model>
-__global__ void __launch_bounds__(32, 16) solve_kernel(const __grid_constant__ SolverParams P,
+__global__ void __launch_bounds__(32, PANTR_MIN_BLOCKS) solve_kernel(const __grid_constant__ SolverParams P,
                                                    const __grid_constant__ KernelArgs A) {
     __shared__ IterScalars it[3];
     double *ws = A.ws + size_t(blockIdx.x) * A.ws_stride;

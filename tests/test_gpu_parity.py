@@ -69,3 +69,40 @@ def test_hanging_chain_solve_parity(pb, N, B):
         if b == 0:  # iteration-level parity (the arithmetic is designed to be bit-identical)
             assert len(tro) == len(trace)
             np.testing.assert_array_equal(tro, trace)
+
+
+def test_closed_loop_driver_matches_oracle_closed_loop(pb, tmp_path, monkeypatch):
+    """Batched mpc_driver (device-resident closed loop) vs the reference's closed loop
+    (drivers/mpc-driver.cpp:123-210) executed with the CPU oracle, instance 0 = the reference run."""
+    import importlib.util
+    from pantr_cdc2023_experiments_b200 import mpc_driver
+    N, num_sim = 10, 4
+    monkeypatch.chdir(tmp_path)
+    opts = pb.benchmark_options("hanging_chain") + [f"num_sim={num_sim}", "warm=1", "batch=3", "results_name=results_cl"]
+    assert mpc_driver.run(["/some/dir/hanging_chain", str(N), "ss2p"] + opts) == 0
+    spec = importlib.util.spec_from_file_location("", str(tmp_path / "results_cl.py"))
+    mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
+    res = mod.results
+    assert res["states"].shape == (57, num_sim + 1) and res["inputs"].shape == (3 * N, num_sim)
+    assert res["batch_size"] == 3 and res["nvar"] == 3 * N and res["ncon"] == 0
+    # oracle closed loop
+    solver, _ = pb.make_solver(opts)
+    par = ou.pack_params(solver)
+    x = np.zeros(57); x[0:30:3] = (np.arange(10) + 1) / 10
+    for _ in range(5):
+        x = ou.simulate(0, x, np.array([-1.0, 1.0, 1.0]))            # num_dist=5 u_dist=-1,1,1
+    u, _, _, _ = ou.solve(0, N, par, x, np.zeros(3 * N))
+    x = ou.simulate(0, x, u[:3])
+    evals_hvp = 0
+    for i in range(num_sim):
+        u = np.concatenate([u[3:], u[-3:]])                             # mpc-driver.cpp:170
+        u, _, so, _ = ou.solve(0, N, par, x, u)
+        assert so["status"] == 1 and res["runtimes"][i] > 0
+        np.testing.assert_array_equal(res["states"][:, i], x)
+        np.testing.assert_array_equal(res["inputs"][:, i], u)
+        evals_hvp += int(so["ev_hess_psi_prod"])
+        x = ou.simulate(0, x, u[:3])
+    np.testing.assert_array_equal(res["states"][:, num_sim], x)
+    assert res["evaluations"]["hess_ψ_prod"] == evals_hvp
+    batch = np.load(tmp_path / "results_cl.npz")
+    assert batch["states"].shape == (3, 57, num_sim + 1) and (batch["runtimes"] > 0).all()
