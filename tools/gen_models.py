@@ -1,0 +1,158 @@
+#!/usr/bin/env python
+"""Generates the straight-line model code of the two quadcopter problems with sympy
+(the reference generates its problem functions with CasADi: problems/generate_problem.py,
+alpaqa/python/alpaqa/casadi_generator/__init__.py:50-190; CasADi is not available here).
+
+Math spec (reference, paths relative to /root/reference/python/alpaqa_mpc_benchmarks):
+  problems/quadcopter.py:17-47            f_c of the simplified quadcopter, ZYX rotation matrix
+  problems/realistic_quadcopter.py:17-52  f_c of the realistic quadcopter, ARB and Omega^-1 omega
+  problems/quadcopter.py:62-75            stage/terminal constraint c(x) (same in both files)
+
+For f_c: R^9 x R^4 -> R^9 and c: R^9 -> R^4 it emits, as `PANTR_HD inline` functions,
+  <f>(z) ; <f>_jvp(z, dz) = J dz ; <f>_vjp(z, w) = J^T w ; <f>_hvjp(z, w, dz) = d/dz[J^T w] dz
+with the sines/cosines of the three angles passed in as `sc[6]` (they are computed once per stage
+point by pantr_sincos and cached by the rollout).  The same header is compiled into the CUDA
+library and into the CPU oracle, so both evaluate identical operation sequences.
+
+Usage: python tools/gen_models.py   (writes pantr_cdc2023_experiments_b200/csrc/generated/*.h)
+"""
+import os
+
+import sympy as sp
+from sympy.printing.c import C99CodePrinter
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(os.path.dirname(HERE), "pantr_cdc2023_experiments_b200", "csrc", "generated")
+
+x = sp.symbols("x0:9", real=True)
+u = sp.symbols("u0:4", real=True)
+dx = sp.symbols("dx0:9", real=True)
+du = sp.symbols("du0:4", real=True)
+w = sp.symbols("w0:9", real=True)
+yh = sp.symbols("yh0:4", real=True)
+S = sp.symbols("sc0 sc2 sc4", real=True)   # sines of x6, x7, x8
+Cc = sp.symbols("sc1 sc3 sc5", real=True)  # cosines
+TRIG = {}
+for i in range(3):
+    TRIG[sp.sin(x[6 + i])] = S[i]
+    TRIG[sp.cos(x[6 + i])] = Cc[i]
+G = sp.Float(9.81)
+
+
+def fc_quadcopter():
+    """quadcopter.py:30-47"""
+    p, v, th = x[0:3], x[3:6], x[6:9]
+    at, om = u[0], u[1:4]
+    cr, sr, cp, sp_, cy, sy = sp.cos(th[0]), sp.sin(th[0]), sp.cos(th[1]), sp.sin(th[1]), sp.cos(th[2]), sp.sin(th[2])
+    R = sp.Matrix([[cy * cp, cy * sp_ * sr - sy * cr, cy * sp_ * cr + sy * sr],
+                   [sy * cp, sy * sp_ * sr + cy * cr, sy * sp_ * cr - cy * sr],
+                   [-sp_, cp * sr, cp * cr]])
+    a = R * sp.Matrix([0, 0, at]) + sp.Matrix([0, 0, -G])
+    return list(v) + list(a) + list(om)
+
+
+def fc_realistic_quadcopter():
+    """realistic_quadcopter.py:29-52 (orient = (phi, theta, psi) = x6, x7, x8)"""
+    v = x[3:6]
+    phi, th, psi = x[6], x[7], x[8]
+    at, om = u[0], sp.Matrix(u[1:4])
+    cpsi, cphi, cth = sp.cos(psi), sp.cos(phi), sp.cos(th)
+    spsi, sphi, sth = sp.sin(psi), sp.sin(phi), sp.sin(th)
+    ARB = sp.Matrix([[cpsi * cth - sphi * spsi * sth, -cphi * spsi, cpsi * sth + cth * sphi * spsi],
+                     [cth * spsi + cpsi * sphi * sth, cphi * cpsi, spsi * sth - cpsi * cth * sphi],
+                     [-cphi * sth, sphi, cphi * cth]])
+    Om = sp.Matrix([[cth, 0, -cphi * sth], [0, 1, sphi], [sth, 0, cphi * cth]])
+    d_orient = sp.simplify(Om.LUsolve(om))
+    a = ARB * sp.Matrix([0, 0, at]) + sp.Matrix([0, 0, -G])
+    return list(v) + list(a) + list(d_orient)
+
+
+def constraints():
+    """quadcopter.py:62-69"""
+    return [x[6], x[7], sp.cos(x[6]) * sp.cos(x[7]), sp.Float(0.1) ** 2 - x[0] ** 2 - x[1] ** 2]
+
+
+class Printer(C99CodePrinter):
+    def _print_Pow(self, e):
+        if e.exp.is_Integer and 1 < int(e.exp) <= 4:
+            b = self._print(e.base)
+            if not e.base.is_Atom:
+                b = "(" + b + ")"
+            return "(" + "*".join([b] * int(e.exp)) + ")"
+        if e.exp == -1:
+            return "(1.0/" + self.parenthesize(e.base, 100) + ")"
+        if e.exp.is_Integer and -4 <= int(e.exp) < -1:
+            b = self._print(e.base)
+            if not e.base.is_Atom:
+                b = "(" + b + ")"
+            return "(1.0/(" + "*".join([b] * (-int(e.exp))) + "))"
+        return super()._print_Pow(e)
+
+
+PR = Printer({"precision": 17})
+
+
+def emit(name, args, outs, exprs):
+    """args: list of (c_name, symbols); outs: list of (c_name, n); exprs: flat list of sympy exprs."""
+    exprs = [sp.sympify(e).subs(TRIG) for e in exprs]
+    for e in exprs:
+        assert not e.has(sp.sin) and not e.has(sp.cos), e
+    repl, red = sp.cse(exprs, symbols=sp.numbered_symbols("t"), order="canonical")
+    used = set().union(*[e.free_symbols for e in exprs]) if exprs else set()
+    sig = ", ".join(f"const double *{a}" for a, _ in args) + ", " + ", ".join(f"double *{o}" for o, _ in outs)
+    lines = [f"PANTR_HD inline void {name}({sig}) {{"]
+    for a, syms in args:
+        for i, s in enumerate(syms):
+            if s in used:
+                lines.append(f"    const double {s} = {a}[{i}];")
+    for a, _ in args:
+        lines.append(f"    (void){a};")
+    for s, e in repl:
+        lines.append(f"    const double {s} = {PR.doprint(e)};")
+    k = 0
+    for o, n in outs:
+        for i in range(n):
+            lines.append(f"    {o}[{i}] = {PR.doprint(red[k])};")
+            k += 1
+    lines.append("}")
+    return "\n".join(lines)
+
+
+def family(prefix, F, zvars, dzvars, zargs, dzargs, wsyms, wname, outs):
+    """value, jvp, vjp, hvjp of F(z).  outs: list of (name, n) splitting the z-gradient outputs."""
+    F = [sp.sympify(f) for f in F]
+    n = len(F)
+    J = sp.Matrix(F).jacobian(sp.Matrix(zvars))
+    sc_arg = [("sc", list(S[:1]) + list(Cc[:1]) + list(S[1:2]) + list(Cc[1:2]) + list(S[2:]) + list(Cc[2:]))]
+    parts = []
+    parts.append(emit(prefix, zargs + sc_arg, [("k", n)], F))
+    parts.append(emit(prefix + "_jvp", zargs + sc_arg + dzargs, [("dk", n)], list(J * sp.Matrix(dzvars))))
+    g = sum(wi * fi for wi, fi in zip(wsyms, F))
+    grad = [sp.diff(g, z) for z in zvars]
+    parts.append(emit(prefix + "_vjp", zargs + sc_arg + [(wname, wsyms)], [("a" + o, k) for o, k in outs], grad))
+    hv = [sum(sp.diff(gi, zj) * dzj for zj, dzj in zip(zvars, dzvars)) for gi in grad]
+    parts.append(emit(prefix + "_hvjp", zargs + sc_arg + [(wname, wsyms)] + dzargs, [("b" + o, k) for o, k in outs], hv))
+    return "\n\n".join(parts)
+
+
+def write_model(ns, fc, ref):
+    body = family("fc", fc, list(x) + list(u), list(dx) + list(du), [("x", x), ("u", u)], [("dx", dx), ("du", du)],
+                  w, "w", [("x", 9), ("u", 4)])
+    body += "\n\n" + family("con", constraints(), list(x), list(dx), [("x", x)], [("dx", dx)], yh, "yh", [("x", 9)])
+    text = (f"// GENERATED by tools/gen_models.py (sympy {sp.__version__}) -- do not edit.\n"
+            f"// Model: {ref}\n"
+            "// fc: continuous dynamics f_c(x, u); con: stage/terminal constraint c(x).  sc = {sin x6, cos x6,\n"
+            "// sin x7, cos x7, sin x8, cos x8}.  *_jvp = J dz, *_vjp = J^T w, *_hvjp = d/dz[J^T w] dz.\n"
+            "#pragma once\n#include \"../pantr_hd.h\"\n\n"
+            f"namespace pantr {{\nnamespace {ns} {{\n\n{body}\n\n}} // namespace {ns}\n}} // namespace pantr\n")
+    path = os.path.join(OUT, f"{ns}.h")
+    with open(path, "w") as fh:
+        fh.write(text)
+    print("wrote", path, len(text.splitlines()), "lines")
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    write_model("quadcopter_gen", fc_quadcopter(), "python/alpaqa_mpc_benchmarks/problems/quadcopter.py:17-75")
+    write_model("realistic_quadcopter_gen", fc_realistic_quadcopter(),
+                "python/alpaqa_mpc_benchmarks/problems/realistic_quadcopter.py:17-75")
