@@ -63,6 +63,8 @@ def fc_realistic_quadcopter():
                      [-cphi * sth, sphi, cphi * cth]])
     Om = sp.Matrix([[cth, 0, -cphi * sth], [0, 1, sphi], [sth, 0, cphi * cth]])
     d_orient = sp.simplify(Om.LUsolve(om))
+    # keep only sin/cos of the angles (they are passed in as sc[]): no tan in the emitted code
+    d_orient = d_orient.applyfunc(lambda e: e.replace(sp.tan, lambda a: sp.sin(a) / sp.cos(a)))
     a = ARB * sp.Matrix([0, 0, at]) + sp.Matrix([0, 0, -G])
     return list(v) + list(a) + list(d_orient)
 
@@ -96,7 +98,7 @@ def emit(name, args, outs, exprs):
     """args: list of (c_name, symbols); outs: list of (c_name, n); exprs: flat list of sympy exprs."""
     exprs = [sp.sympify(e).subs(TRIG) for e in exprs]
     for e in exprs:
-        assert not e.has(sp.sin) and not e.has(sp.cos), e
+        assert not e.has(sp.sin) and not e.has(sp.cos) and not e.has(sp.tan), e
     repl, red = sp.cse(exprs, symbols=sp.numbered_symbols("t"), order="canonical")
     used = set().union(*[e.free_symbols for e in exprs]) if exprs else set()
     sig = ", ".join(f"const double *{a}" for a, _ in args) + ", " + ", ".join(f"double *{o}" for o, _ in outs)
