@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_core.hpp header).
 // C entry points for ctypes (tests/, smoke(), bench.py cpu_baseline / --impl reference).
 #include "hanging_chain.hpp"
+#include "quadcopter.hpp"
 #include "generic_problems.hpp"
 #include "oracle_alm.hpp"
 #include <atomic>
@@ -17,12 +18,16 @@ constexpr int NPARAMS = 48, NSTATS = 24;
 std::unique_ptr<Problem> make_problem(int problem_id, int N) {
     switch (problem_id) {
         case 0: return std::make_unique<HangingChain>(N);
+        case 1: return std::make_unique<SimpleQuadcopter>(N);
+        case 2: return std::make_unique<RealisticQuadcopter>(N);
         default: return nullptr;
     }
 }
 int nx_of(int problem_id) { return problem_id == 0 ? HangingChain::NX : 9; }
 void set_x0(Problem &p, int problem_id, const double *x0) {
     if (problem_id == 0) { auto &hc = static_cast<HangingChain &>(p); std::copy(x0, x0 + hc.NX, hc.x0.begin()); }
+    if (problem_id == 1) { auto &q = static_cast<SimpleQuadcopter &>(p); std::copy(x0, x0 + 9, q.x0.begin()); }
+    if (problem_id == 2) { auto &q = static_cast<RealisticQuadcopter &>(p); std::copy(x0, x0 + 9, q.x0.begin()); }
 }
 
 ALMSolver make_solver(const double *P) {
@@ -75,6 +80,21 @@ int oracle_dims(int problem_id, int N, long *dims) {
     return 0;
 }
 
+// f and g = [c(x_0); ...; c(x_N)] at u (TypeErasedProblem::eval_f / eval_g)
+int oracle_eval_f_g(int problem_id, int N, const double *x0, const double *u, double *f, double *g) {
+    auto p = make_problem(problem_id, N);
+    if (!p) return -1;
+    set_x0(*p, problem_id, x0);
+    *f = p->eval_f(u);
+    if (g && p->m) p->eval_g(u, g);
+    return 0;
+}
+
+// sin/cos restatement shared with the CUDA path (csrc/pantr_hd.h)
+void oracle_sincos(long n, const double *x, double *s, double *c) {
+    for (long i = 0; i < n; ++i) pantr::pantr_sincos(x[i], s + i, c + i);
+}
+
 // Evaluate psi, grad psi, yhat and (if v) hess_psi_prod at (u, y, Sigma) for initial state x0.
 int oracle_eval(int problem_id, int N, const double *x0, const double *u, const double *y,
                 const double *Sigma, const double *v, double *psi, double *grad, double *yhat,
@@ -90,10 +110,10 @@ int oracle_eval(int problem_id, int N, const double *x0, const double *u, const 
 
 // Plant step x+ = f_d(x, u): problems/problems/formulation.hpp:258-261
 int oracle_simulate_dynamics(int problem_id, const double *x, const double *u, double *xn) {
-    if (problem_id != 0) return -1;
-    HangingChain hc(1);
-    hc.rk4(x, u, xn);
-    return 0;
+    if (problem_id == 0) { HangingChain hc(1); hc.rk4(x, u, xn); return 0; }
+    if (problem_id == 1) { pantr::quad::rk4<pantr::quad::SimpleGen>(x, u, xn, nullptr); return 0; }
+    if (problem_id == 2) { pantr::quad::rk4<pantr::quad::RealisticGen>(x, u, xn, nullptr); return 0; }
+    return -1;
 }
 
 // One ALM+PANTR solve.  u (n) and y (m) are in/out.  trace (optional): max_trace rows of 11 doubles.
