@@ -350,6 +350,10 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
 // Problem-function surface the solver sees (what CasADiProblem::eval_* would compute, m = 0).
 struct HangingChain {
     static constexpr int NX = hc::NX, NU = hc::NU, NC = 0;
+#ifndef PANTR_MIN_BLOCKS
+#define PANTR_MIN_BLOCKS 16 // resident warps per SM the solve kernel is compiled for (128 registers)
+#endif
+    static constexpr int MIN_BLOCKS = PANTR_MIN_BLOCKS;
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int) { return 0; }
     // traj + dtraj + iwc
@@ -371,7 +375,8 @@ struct HangingChain {
     __device__ void init(int N_, const double *x0_, double *ws) {
         N = N_; x0 = x0_; traj = ws; dtraj = ws + (N_ + 1) * NX; iwc = ws + 2 * (N_ + 1) * NX;
     }
-    __device__ void eval_f_g_sqnorm(const double *u, double &f, double &g2) { f = eval_psi(u, nullptr, nullptr, nullptr); g2 = 0; }
+    __device__ double eval_f(const double *u) { return eval_psi(u, nullptr, nullptr, nullptr); }
+    __device__ void eval_g(const double *, double *) {}
     __device__ double eval_psi(const double *x, const double *, const double *, double *) {
         __syncwarp();
         double f = hc::rollout(N, x0, x, traj, iwc);

@@ -61,8 +61,9 @@
             for (int i = lane_id(); i < m; i += 32) S[i] = a.initial_penalty;
         } else { // alm-helpers.tpp:47-59
             ++st.ev_f; ++st.ev_g;
-            double f0, g0sq;
-            mdl.eval_f_g_sqnorm(x, f0, g0sq);
+            double f0 = mdl.eval_f(x);
+            mdl.eval_g(x, e1);
+            double g0sq = vsqnorm(e1, m);
             double sigma = a.initial_penalty_factor * fmax(1.0, fabs(f0)) / fmax(1.0, 0.5 * g0sq);
             sigma = sigma < a.min_penalty ? a.min_penalty : (a.max_penalty < sigma ? a.max_penalty : sigma);
             for (int i = lane_id(); i < m; i += 32) S[i] = sigma;

@@ -3,14 +3,12 @@
 // loop, Steihaug-CG, problem evaluations); blocks are persistent and pull instances from a queue.
 #include "pantr_device.cuh"
 #include "hanging_chain.cuh"
+#include "quadcopter.cuh"
 #include <cstdio>
 #include <cstring>
 #include <string>
 #include <vector>
 
-#ifndef PANTR_MIN_BLOCKS
-#define PANTR_MIN_BLOCKS 16 // resident warps per SM the solve kernel is compiled for (128 registers)
-#endif
 using namespace pantr;
 
 namespace {
@@ -38,7 +36,7 @@ struct KernelArgs {
 
 // ---- the solve kernel: ALMSolver::operator() for every instance of the batch ----
 template <class Model>
-__global__ void __launch_bounds__(32, PANTR_MIN_BLOCKS) solve_kernel(const __grid_constant__ SolverParams P,
+__global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __grid_constant__ SolverParams P,
                                                    const __grid_constant__ KernelArgs A) {
     __shared__ IterScalars it[3];
     double *ws = A.ws + size_t(blockIdx.x) * A.ws_stride;

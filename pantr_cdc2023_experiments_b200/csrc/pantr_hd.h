@@ -8,7 +8,7 @@
 #define PANTR_UNROLL _Pragma("unroll")
 #define PANTR_NOUNROLL _Pragma("unroll 1")
 #else
-#define PANTR_HD
+#define PANTR_HD inline
 #define PANTR_UNROLL _Pragma("GCC unroll 16")
 #define PANTR_NOUNROLL _Pragma("GCC unroll 1")
 #endif
@@ -21,7 +21,7 @@ namespace pantr {
 /// parity tolerance).  Three-term Cody-Waite reduction by pi/2 (exact products for |x| < 1.6e6,
 /// the constants carry 33 bits each) and the classic degree-13/14 minimax kernels on [-pi/4, pi/4].
 /// |x| >= 1.6e6 or non-finite x gives NaN (the solver then reports NotFinite).
-PANTR_HD inline void pantr_sincos(double x, double *s, double *c) {
+PANTR_HD void pantr_sincos(double x, double *s, double *c) {
     if (!(fabs(x) < 1.6e6)) { *s = x - x; *c = x - x; if (*s == 0) { *s = NAN; *c = NAN; } return; }
     const double fn = rint(x * 6.36619772367581382433e-01);
     const int q = (int)fn;

@@ -1,0 +1,84 @@
+// The two quadcopter MPC models as seen by the device solver (what CasADiProblem::eval_* computes
+// for quadcopter_ss2p_<N> / realistic_quadcopter_ss2p_<N>; m = 4(N+1) general constraints, so
+// these exercise the ALM outer loop on the device).  The sweeps themselves are the shared
+// host/device code of quadcopter_sweeps.h; with nx = 9 there is no intra-instance parallelism
+// worth a shuffle, so the 32 lanes of the owning warp execute them redundantly (uniform loads and
+// stores) and only the O(n) solver vector work is lane-strided.
+#pragma once
+#include "quadcopter_sweeps.h"
+#include "warp_utils.cuh"
+
+namespace pantr {
+
+template <class G>
+struct QuadcopterModel {
+    static constexpr int NX = quad::NX, NU = quad::NU, NC = quad::NC;
+    static constexpr int MIN_BLOCKS = 8; // resident warps per SM the solve kernel is compiled for
+    __host__ __device__ static int n(int N) { return NU * N; }
+    __host__ __device__ static int m(int N) { return NC * (N + 1); }
+    __host__ __device__ static int traj_doubles(int N) { return quad::QuadWS::doubles(N); }
+    __host__ __device__ static double C_lb(int i) { return quad::C_lb(i); } // quadcopter.py:56-59, ss.py:28-29
+    __host__ __device__ static double C_ub(int i) { return quad::C_ub(i); }
+    __host__ __device__ static double D_lb(int i, int) { return quad::D_lb(i); } // quadcopter.py:70-73, ss.py:41-42
+    __host__ __device__ static double D_ub(int i, int) { return quad::D_ub(i); }
+    static void initial_state(double *x) { // quadcopter.py:78-83
+        for (int i = 0; i < NX; ++i) x[i] = 0;
+        x[0] = -0.2; x[1] = -0.25; x[2] = 0.5;
+    }
+    static void initial_guess(double *u, int N) { // quadcopter.py:112
+        for (int k = 0; k < N; ++k) { u[4 * k] = 9.81; u[4 * k + 1] = u[4 * k + 2] = u[4 * k + 3] = 0; }
+    }
+
+    int N;
+    const double *x0;
+    quad::QuadWS w;
+    bool hvp_ready;
+
+    __device__ void init(int N_, const double *x0_, double *ws) { N = N_; x0 = x0_; w.bind(ws, N_); hvp_ready = false; }
+    __device__ __noinline__ double eval_f(const double *u) {
+        __syncwarp();
+        hvp_ready = false;
+        double f = quad::rollout<G>(N, x0, u, w);
+        __syncwarp();
+        return f;
+    }
+    __device__ __noinline__ void eval_g(const double *u, double *g) {
+        (void)eval_f(u);
+        quad::constraints<G>(N, w, g);
+        __syncwarp();
+    }
+    __device__ __noinline__ double eval_psi(const double *x, const double *y, const double *S, double *yhat) {
+        double f   = eval_f(x);
+        double psi = f + quad::al_terms<G>(N, w, y, S, yhat, nullptr);
+        __syncwarp();
+        return psi;
+    }
+    __device__ __noinline__ double eval_psi_grad_psi(const double *x, const double *y, const double *S, double *grad) {
+        double f   = eval_f(x);
+        double psi = f + quad::al_terms<G>(N, w, y, S, w.yh, w.wact);
+        quad::adjoint<G>(N, x, w, grad);
+        hvp_ready = true;
+        __syncwarp();
+        return psi;
+    }
+    __device__ __noinline__ void hess_psi_prod(const double *x, const double *y, const double *S, const double *v,
+                                               double *Hv) {
+        __syncwarp();
+        if (!hvp_ready) (void)eval_psi_grad_psi(x, y, S, Hv);
+        quad::hvp<G>(N, x, v, w, Hv);
+        __syncwarp();
+    }
+    /// Plant step x+ = f_d(x, u) (problems/problems/formulation.hpp:258-261)
+    __device__ static void plant_step(const double *x, const double *u, double *xn) {
+        double xx[NX], uu[NU], o[NX];
+        for (int i = 0; i < NX; ++i) xx[i] = x[i];
+        for (int j = 0; j < NU; ++j) uu[j] = u[j];
+        quad::rk4<G>(xx, uu, o, nullptr);
+        for (int i = 0; i < NX; ++i) xn[i] = o[i];
+    }
+};
+
+using Quadcopter          = QuadcopterModel<quad::SimpleGen>;
+using RealisticQuadcopter = QuadcopterModel<quad::RealisticGen>;
+
+} // namespace pantr

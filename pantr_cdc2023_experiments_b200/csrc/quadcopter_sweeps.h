@@ -34,11 +34,11 @@ constexpr double qN_v = 25 * q_v, qN_p = 25 * q_p, qN_th = 10 * q_th;
 constexpr double at_max = 9.81 * 5, dtilt_max = 0.1;
 constexpr double half_pi = 1.5707963267948966, cos_tilt_max = 0.85252452205950568; // cos(1.1 / 2)
 
-PANTR_HD inline double pf(int i) { return i == 2 ? 0.5 : 0.25; }
-PANTR_HD inline double C_lb(int i) { return (i & 3) == 0 ? 0.0 : -dtilt_max; }
-PANTR_HD inline double C_ub(int i) { return (i & 3) == 0 ? at_max : dtilt_max; }
-PANTR_HD inline double D_lb(int i) { return (i & 3) < 2 ? -half_pi : ((i & 3) == 2 ? cos_tilt_max : -INFINITY); }
-PANTR_HD inline double D_ub(int i) { return (i & 3) < 2 ? half_pi : ((i & 3) == 2 ? INFINITY : 0.0); }
+PANTR_HD double pf(int i) { return i == 2 ? 0.5 : 0.25; }
+PANTR_HD double C_lb(int i) { return (i & 3) == 0 ? 0.0 : -dtilt_max; }
+PANTR_HD double C_ub(int i) { return (i & 3) == 0 ? at_max : dtilt_max; }
+PANTR_HD double D_lb(int i) { return (i & 3) < 2 ? -half_pi : ((i & 3) == 2 ? cos_tilt_max : -INFINITY); }
+PANTR_HD double D_ub(int i) { return (i & 3) < 2 ? half_pi : ((i & 3) == 2 ? INFINITY : 0.0); }
 
 #define PANTR_QUAD_GEN(Name, ns)                                                                             \
     struct Name {                                                                                            \
@@ -83,28 +83,28 @@ struct QuadWS {
     }
 };
 
-PANTR_HD inline void sincos3(const double *x, double *sc) {
+PANTR_HD void sincos3(const double *x, double *sc) {
     pantr_sincos(x[6], &sc[0], &sc[1]);
     pantr_sincos(x[7], &sc[2], &sc[3]);
     pantr_sincos(x[8], &sc[4], &sc[5]);
 }
-PANTR_HD inline double sq3(double a, double b, double c) { return (a * a + b * b) + c * c; }
-PANTR_HD inline double stage_cost(const double *x, const double *u) {
+PANTR_HD double sq3(double a, double b, double c) { return (a * a + b * b) + c * c; }
+PANTR_HD double stage_cost(const double *x, const double *u) {
     double lu = r_u * ((u[0] * u[0] + u[1] * u[1]) + (u[2] * u[2] + u[3] * u[3])) + r_om * sq3(u[1], u[2], u[3]);
     double lx = (q_v * sq3(x[3], x[4], x[5]) + q_p * sq3(x[0] - pf(0), x[1] - pf(1), x[2] - pf(2))) +
                 q_th * sq3(x[6], x[7], x[8]);
     return lu + lx;
 }
-PANTR_HD inline double term_cost(const double *x) {
+PANTR_HD double term_cost(const double *x) {
     return (qN_v * sq3(x[3], x[4], x[5]) + qN_p * sq3(x[0] - pf(0), x[1] - pf(1), x[2] - pf(2))) +
            qN_th * sq3(x[6], x[7], x[8]);
 }
 /// weight of state entry i in the (diagonal) cost Hessian / 2
-PANTR_HD inline double qx(int i, bool term) {
+PANTR_HD double qx(int i, bool term) {
     return i < 3 ? (term ? qN_p : q_p) : (i < 6 ? (term ? qN_v : q_v) : (term ? qN_th : q_th));
 }
-PANTR_HD inline double ru(int j) { return j == 0 ? r_u : r_u + r_om; }
-PANTR_HD inline double dcost_x(const double *x, int i, bool term) {
+PANTR_HD double ru(int j) { return j == 0 ? r_u : r_u + r_om; }
+PANTR_HD double dcost_x(const double *x, int i, bool term) {
     return (2 * qx(i, term)) * (i < 3 ? x[i] - pf(i) : x[i]);
 }
 

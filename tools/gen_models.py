@@ -102,7 +102,7 @@ def emit(name, args, outs, exprs):
     repl, red = sp.cse(exprs, symbols=sp.numbered_symbols("t"), order="canonical")
     used = set().union(*[e.free_symbols for e in exprs]) if exprs else set()
     sig = ", ".join(f"const double *{a}" for a, _ in args) + ", " + ", ".join(f"double *{o}" for o, _ in outs)
-    lines = [f"PANTR_HD inline void {name}({sig}) {{"]
+    lines = [f"PANTR_HD void {name}({sig}) {{"]
     for a, syms in args:
         for i, s in enumerate(syms):
             if s in used:
