@@ -106,3 +106,93 @@ def test_closed_loop_driver_matches_oracle_closed_loop(pb, tmp_path, monkeypatch
     assert res["evaluations"]["hess_ψ_prod"] == evals_hvp
     batch = np.load(tmp_path / "results_cl.npz")
     assert batch["states"].shape == (3, 57, num_sim + 1) and (batch["runtimes"] > 0).all()
+
+
+# ---- quadcopter / realistic quadcopter: m = 4(N+1) > 0, the ALM loop runs on the device ----
+QUADS = [("quadcopter", 1), ("realistic_quadcopter", 2)]
+
+
+def quad_states(B, rng):
+    """x0 = (p0 + U[-0.1,0.1]^3, v ~ U[-0.5,0.5]^3, theta ~ U[-0.2,0.2]^3)."""
+    x0 = np.zeros((B, 9))
+    x0[:, :3] = np.array([-0.2, -0.25, 0.5]) + rng.uniform(-0.1, 0.1, (B, 3))
+    x0[:, 3:6] = rng.uniform(-0.5, 0.5, (B, 3))
+    x0[:, 6:9] = rng.uniform(-0.2, 0.2, (B, 3))
+    return x0
+
+
+@pytest.mark.parametrize("name,pid", QUADS)
+@pytest.mark.parametrize("N", [1, 7, 60])
+def test_quadcopter_eval_bit_exact(pb, name, pid, N):
+    prob = pb.BatchedProblem(name, N)
+    assert (prob.n, prob.m, prob.nx, prob.nu, prob.nc) == (4 * N, 4 * N + 4, 9, 4, 4)
+    rng = np.random.default_rng(7 * pid + N)
+    B = 5
+    x0 = quad_states(B, rng)
+    u = np.tile(prob.initial_guess(), (B, 1)) + rng.uniform(-0.1, 0.1, (B, prob.n)) * np.tile([30, 1, 1, 1], N)
+    y = rng.standard_normal((B, prob.m)) * 5
+    S = 10.0 ** rng.uniform(0, 3, (B, prob.m))
+    v = rng.standard_normal((B, prob.n))
+    psi, grad, yhat, Hv = prob.eval(x0, u, y=y, Sigma=S, v=v, want_yhat=True)
+    for b in range(B):
+        po, go, yo, Ho = ou.eval_(pid, N, x0[b], u[b], y=y[b], Sigma=S[b], v=v[b], want_yhat=True)
+        assert po == psi[b]
+        np.testing.assert_array_equal(go, grad[b])
+        np.testing.assert_array_equal(yo, yhat[b])
+        np.testing.assert_array_equal(Ho, Hv[b])
+    # Hessian-vector product alone (no gradient requested): the model refreshes its adjoint cache
+    _, _, _, Hv2 = prob.eval(x0, u, y=y, Sigma=S, v=v, want_grad=False)
+    np.testing.assert_array_equal(Hv2, Hv)
+
+
+@pytest.mark.parametrize("name,pid", QUADS)
+def test_quadcopter_plant_step_and_boxes(pb, name, pid):
+    prob = pb.BatchedProblem(name, 5)
+    rng = np.random.default_rng(pid)
+    x = quad_states(4, rng)
+    u = np.tile([9.81, 0, 0, 0], (4, 1)) + rng.uniform(-0.1, 0.1, (4, 4))
+    xn = prob.simulate_dynamics(x, u)
+    for b in range(4):
+        np.testing.assert_array_equal(ou.simulate(pid, x[b], u[b]), xn[b])
+    lb, ub = prob.get_box_C()
+    np.testing.assert_array_equal(lb, np.tile([0, -0.1, -0.1, -0.1], 5))
+    np.testing.assert_array_equal(ub, np.tile([9.81 * 5, 0.1, 0.1, 0.1], 5))
+    zl, zu = prob.get_box_D()
+    np.testing.assert_array_equal(zl, np.tile([-np.pi / 2, -np.pi / 2, np.cos(1.1 / 2), -np.inf], 6))
+    np.testing.assert_array_equal(zu, np.tile([np.pi / 2, np.pi / 2, np.inf, 0], 6))
+    np.testing.assert_array_equal(prob.initial_state(), [-0.2, -0.25, 0.5, 0, 0, 0, 0, 0, 0])
+
+
+@pytest.mark.parametrize("name,pid", QUADS)
+@pytest.mark.parametrize("N,B", [(10, 6), (30, 3)])
+def test_quadcopter_solve_parity(pb, name, pid, N, B):
+    solver, _ = pb.make_solver(pb.benchmark_options(name))
+    prob = pb.BatchedProblem(name, N)
+    rng = np.random.default_rng(200 + 10 * pid + N)
+    x0 = quad_states(B, rng)
+    x0[0] = prob.initial_state()  # instance 0 = the reference's own cold start
+    u = np.tile(prob.initial_guess(), (B, 1))
+    y = np.zeros((B, prob.m))
+    solver.set_trace(prob, 0, 8192)
+    stats = solver(prob, u, y, x0=x0)
+    trace = solver.get_trace(prob, 8192)
+    par = ou.pack_params(solver)
+    for b in range(B):
+        uo, yo, so, tro = ou.solve(pid, N, par, x0[b], prob.initial_guess(), trace_rows=8192 if b == 0 else 0)
+        assert int(so["status"]) == stats["status"][b]
+        assert abs(int(so["outer_iterations"]) - int(stats["outer_iterations"][b])) <= 1
+        assert abs(int(so["inner_iterations"]) - int(stats["inner_iterations"][b])) <= 1
+        np.testing.assert_allclose(u[b], uo, rtol=1e-8, atol=1e-10)
+        np.testing.assert_allclose(y[b], yo, rtol=1e-8, atol=1e-8)
+        np.testing.assert_allclose(stats["final_psi"][b], so["final_psi"], rtol=1e-8)
+        np.testing.assert_allclose(stats["delta"][b], so["delta"], rtol=1e-6, atol=1e-12)
+        np.testing.assert_allclose(stats["norm_penalty"][b], so["norm_penalty"], rtol=1e-12)
+        for k in ("ev_psi", "ev_psi_grad_psi", "ev_grad_L", "ev_hess_psi_prod", "ev_prox_grad_step",
+                  "ev_grad_psi", "ev_inactive_indices_res_lna", "ev_proj_multipliers"):
+            assert abs(int(so[k]) - int(stats[k][b])) <= max(2, 0.02 * so[k]), k
+        if b == 0:  # same arithmetic on both sides: iteration-level parity
+            assert len(tro) == len(trace)
+            np.testing.assert_array_equal(tro, trace)
+            np.testing.assert_array_equal(u[b], uo)
+            np.testing.assert_array_equal(y[b], yo)
+    assert (stats["status"] == 1).all()
