@@ -16,6 +16,10 @@
 //                      adjoint and Hessian-vector sweeps rebuild the stage points from it without any
 //                      sqrt / division (same bits as recomputing: identical operations on identical
 //                      inputs), which is what keeps them FP64-add/mul bound.
+//   adjc  N x 4 x 40   first-order adjoint data of every stage point (Fbar per lane, dist . Fbar per
+//                      link), written by the adjoint sweep: they depend on u only, and PANTR takes
+//                      ~30 Hessian-vector products per gradient, so the products' reverse sweep reads
+//                      them instead of carrying the lambda recurrence (no vjp, 25 % fewer instructions).
 // The three sweeps are __noinline__ so that the solver contains exactly one copy of each: the
 // solve kernel's code then fits the SM instruction caches (the fully inlined version was 1.1 MB of
 // SASS and stalled 14 of 19 cycles per issue on instruction fetch: profiles/r01_v0_*).
@@ -162,6 +166,27 @@ __device__ __forceinline__ IW load_iw(const Lane &L, const double *iwc, int k) {
     const double *p = iwc + k * (4 * NLINK) + L.link;
     return IW{p[0], p[NLINK], p[2 * NLINK], p[3 * NLINK]};
 }
+__device__ __forceinline__ void prefetch_iw(const Lane &L, const double *iwc, int k) {
+    if (L.l < 4) {
+        const double *p = iwc + k * (4 * NLINK) + (L.l < 3 ? 16 * L.l : 4 * NLINK - 1);
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+    }
+}
+// Per-stage caches, 40 doubles per stage point (4 per RK4 step): entries 0..29 are lane values,
+// 30..39 the per-link scalars (written by the link's base lane).
+constexpr int SC = NL + NLINK, SCSTEP = 4 * SC;
+__device__ __forceinline__ void store_sc(const Lane &L, double *c, double lanev, double linkv) {
+    if (L.active) c[L.l] = lanev;
+    if (L.active && L.l == L.base) c[NL + L.link] = linkv;
+}
+__device__ __forceinline__ void load_sc(const Lane &L, const double *c, double &lanev, double &linkv) {
+    lanev = L.active ? c[L.l] : 0.0;
+    linkv = c[NL + L.link];
+}
+/// pulls the 10 cache lines of one step's block (160 doubles) into L1
+__device__ __forceinline__ void prefetch_sc(const Lane &L, const double *c) {
+    if (L.l < 10) asm volatile("prefetch.global.L1 [%0];" ::"l"(c + 16 * L.l));
+}
 __device__ __forceinline__ void stages_cached(const Lane &L, double X, double V, double ud, const IW &iw,
                                               Link (&ld)[4], double (&iw2)[4]) {
     double Vu = L.hasV ? V : ud, kX, kV;
@@ -202,10 +227,12 @@ __device__ __noinline__ double rollout(int N, const double *x0, const double *u,
 }
 
 // grad f by discrete adjoint; traj / iwc hold the rollout of `u`
+// Also fills adjc (N x 4 x 40): Fbar (lane) and dist . Fbar (link) of every stage, which depend on
+// u only and are reused by every Hessian-vector product at this u (~30 per gradient).
 __device__ __noinline__ void adjoint(int N, const double *u, const double *traj, const double *iwc,
-                                     double *grad) {
+                                     double *grad, double *adjc) {
     __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(traj)); __builtin_assume(__isGlobal(iwc));
-    __builtin_assume(__isGlobal(grad));
+    __builtin_assume(__isGlobal(grad)); __builtin_assume(__isGlobal(adjc));
     const Lane L;
     double X, V, lX, lV;
     load_state(L, traj, N, X, V);
@@ -224,16 +251,21 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
         stages_cached(L, X, V, ud, iw, ld, iw2);
         double wX, wV, aX, aV, sX, sV, Fb, dt;
         wX = h6 * lX; wV = h6 * lV;
+        double *ac = adjc + k * SCSTEP;
         vjp(L, ld[3], wX, wV, aX, aV, Fb, dt);
+        store_sc(L, ac + 3 * SC, Fb, dt);
         sX = lX + aX; sV = lV + aV;
         wX = h3 * lX + h * aX; wV = h3 * lV + h * aV;
         vjp(L, ld[2], wX, wV, aX, aV, Fb, dt);
+        store_sc(L, ac + 2 * SC, Fb, dt);
         sX = sX + aX; sV = sV + aV;
         wX = h3 * lX + hh * aX; wV = h3 * lV + hh * aV;
         vjp(L, ld[1], wX, wV, aX, aV, Fb, dt);
+        store_sc(L, ac + SC, Fb, dt);
         sX = sX + aX; sV = sV + aV;
         wX = h6 * lX + hh * aX; wV = h6 * lV + hh * aV;
         vjp(L, ld[0], wX, wV, aX, aV, Fb, dt);
+        store_sc(L, ac, Fb, dt);
         sX = sX + aX; sV = sV + aV;
         lX = L.isEnd ? sX + two_alpha * (X - L.ref) : sX;
         if (L.hasV) lV = sV + two_beta * V;
@@ -249,9 +281,10 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
 // casadi_generator/__init__.py:181-189 defines as hess_psi_prod; with m = 0, psi = f).
 // traj / iwc hold the rollout of `u`; dtraj is scratch for the tangent trajectory.
 __device__ __noinline__ void hvp(int N, const double *u, const double *v, const double *traj, double *dtraj,
-                                 const double *iwc, double *Hv) {
+                                 const double *iwc, const double *adjc, double *Hv) {
     __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(v)); __builtin_assume(__isGlobal(traj));
     __builtin_assume(__isGlobal(dtraj)); __builtin_assume(__isGlobal(iwc)); __builtin_assume(__isGlobal(Hv));
+    __builtin_assume(__isGlobal(adjc));
     const Lane L;
     double X, V, dX = 0.0, dV = 0.0;
     // ---- forward tangent sweep ----
@@ -281,67 +314,68 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
         X = Xp; V = Vp; ud = up; vd = vp; iw = iwp;
     }
     __syncwarp();
-    // ---- reverse sweep for lambda and mu = d lambda ----  (X, V = s_N here)
-    double lX, lV, mX, mV;
-    lX = L.isEnd ? two_alpha * (X - L.ref) : 0.0;
+    // ---- reverse sweep for mu = d lambda ----  (X, V = s_N here)
+    // The first-order quantities of every stage (Fbar, dist . Fbar) come from the cache the adjoint
+    // sweep filled at this u: no lambda recurrence and no vjp here.  (Caching the tangent stage
+    // data of the forward sweep as well removes the jvp recomputation but triples the streamed
+    // bytes and measured 6 % slower: profiles/r01_v5_*.)
+    double mX, mV;
     mX = L.isEnd ? two_alpha * dX : 0.0;
-    lV = L.hasV ? two_beta * V : 0.0;
     mV = L.hasV ? two_beta * dV : 0.0;
     load_state(L, traj, N - 1, X, V);
     load_state(L, dtraj, N - 1, dX, dV);
     ud = load_u(L, u, N - 1); vd = load_u(L, v, N - 1);
-    iw = load_iw(L, iwc, N - 1);
 #pragma unroll 1
     for (int k = N - 1; k >= 0; --k) {
+        const double *ac = adjc + k * SCSTEP;
+        double Fb[4], dt[4], ddist[4], dd[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) load_sc(L, ac + j * SC, Fb[j], dt[j]);
+        const IW iw = load_iw(L, iwc, k);
         double Xp = 0, Vp = 0, dXp = 0, dVp = 0, up = 0, vp = 0;
-        IW iwp = iw;
         if (k > 0) {
             load_state(L, traj, k - 1, Xp, Vp); load_state(L, dtraj, k - 1, dXp, dVp);
-            up = load_u(L, u, k - 1); vp = load_u(L, v, k - 1); iwp = load_iw(L, iwc, k - 1);
+            up = load_u(L, u, k - 1); vp = load_u(L, v, k - 1);
+            prefetch_iw(L, iwc, k - 1);
+            prefetch_sc(L, ac - SCSTEP);
         }
         Link ld[4]; double iw2[4];
         stages_cached(L, X, V, ud, iw, ld, iw2);
-        double ddist[4], dd[4];
         {
             double kX, kV;
             jvp(L, ld[0], dX, L.hasV ? dV : vd, kX, kV, ddist[0], dd[0]);
-            double tX = dX + hh * kX, tV = dV + hh * kV;
-            jvp(L, ld[1], tX, L.hasV ? tV : vd, kX, kV, ddist[1], dd[1]);
-            tX = dX + hh * kX; tV = dV + hh * kV;
-            jvp(L, ld[2], tX, L.hasV ? tV : vd, kX, kV, ddist[2], dd[2]);
-            tX = dX + h * kX; tV = dV + h * kV;
-            jvp(L, ld[3], tX, L.hasV ? tV : vd, kX, kV, ddist[3], dd[3]);
+            double sX = dX + hh * kX, sV = dV + hh * kV;
+            jvp(L, ld[1], sX, L.hasV ? sV : vd, kX, kV, ddist[1], dd[1]);
+            sX = dX + hh * kX; sV = dV + hh * kV;
+            jvp(L, ld[2], sX, L.hasV ? sV : vd, kX, kV, ddist[2], dd[2]);
+            sX = dX + h * kX; sV = dV + h * kV;
+            jvp(L, ld[3], sX, L.hasV ? sV : vd, kX, kV, ddist[3], dd[3]);
         }
-        double wX, wV, aX, aV, sX, sV, dwX, dwV, bX, bV, tX, tV, Fb, dt;
+        double dwX, dwV, bX, bV, tX, tV;
         // stage 4
-        wX = h6 * lX; wV = h6 * lV; dwX = h6 * mX; dwV = h6 * mV;
-        vjp(L, ld[3], wX, wV, aX, aV, Fb, dt);
-        hvjp(L, ld[3], iw2[3], Fb, dt, ddist[3], dd[3], dwX, dwV, bX, bV);
-        sX = lX + aX; sV = lV + aV; tX = mX + bX; tV = mV + bV;
+        dwX = h6 * mX; dwV = h6 * mV;
+        hvjp(L, ld[3], iw2[3], Fb[3], dt[3], ddist[3], dd[3], dwX, dwV, bX, bV);
+        tX = mX + bX; tV = mV + bV;
         // stage 3
-        wX = h3 * lX + h * aX; wV = h3 * lV + h * aV; dwX = h3 * mX + h * bX; dwV = h3 * mV + h * bV;
-        vjp(L, ld[2], wX, wV, aX, aV, Fb, dt);
-        hvjp(L, ld[2], iw2[2], Fb, dt, ddist[2], dd[2], dwX, dwV, bX, bV);
-        sX = sX + aX; sV = sV + aV; tX = tX + bX; tV = tV + bV;
+        dwX = h3 * mX + h * bX; dwV = h3 * mV + h * bV;
+        hvjp(L, ld[2], iw2[2], Fb[2], dt[2], ddist[2], dd[2], dwX, dwV, bX, bV);
+        tX = tX + bX; tV = tV + bV;
         // stage 2
-        wX = h3 * lX + hh * aX; wV = h3 * lV + hh * aV; dwX = h3 * mX + hh * bX; dwV = h3 * mV + hh * bV;
-        vjp(L, ld[1], wX, wV, aX, aV, Fb, dt);
-        hvjp(L, ld[1], iw2[1], Fb, dt, ddist[1], dd[1], dwX, dwV, bX, bV);
-        sX = sX + aX; sV = sV + aV; tX = tX + bX; tV = tV + bV;
+        dwX = h3 * mX + hh * bX; dwV = h3 * mV + hh * bV;
+        hvjp(L, ld[1], iw2[1], Fb[1], dt[1], ddist[1], dd[1], dwX, dwV, bX, bV);
+        tX = tX + bX; tV = tV + bV;
         // stage 1
-        wX = h6 * lX + hh * aX; wV = h6 * lV + hh * aV; dwX = h6 * mX + hh * bX; dwV = h6 * mV + hh * bV;
-        vjp(L, ld[0], wX, wV, aX, aV, Fb, dt);
-        hvjp(L, ld[0], iw2[0], Fb, dt, ddist[0], dd[0], dwX, dwV, bX, bV);
-        sX = sX + aX; sV = sV + aV; tX = tX + bX; tV = tV + bV;
+        dwX = h6 * mX + hh * bX; dwV = h6 * mV + hh * bV;
+        hvjp(L, ld[0], iw2[0], Fb[0], dt[0], ddist[0], dd[0], dwX, dwV, bX, bV);
+        tX = tX + bX; tV = tV + bV;
         // stage cost
-        lX = L.isEnd ? sX + two_alpha * (X - L.ref) : sX;
         mX = L.isEnd ? tX + two_alpha * dX : tX;
-        if (L.hasV) { lV = sV + two_beta * V; mV = tV + two_beta * dV; }
+        if (L.hasV) mV = tV + two_beta * dV;
         else {
             if (L.isEnd) Hv[NU * k + (L.l - NVL)] = tV + two_gamma * vd;
-            lV = 0.0; mV = 0.0;
+            mV = 0.0;
         }
-        X = Xp; V = Vp; dX = dXp; dV = dVp; ud = up; vd = vp; iw = iwp;
+        X = Xp; V = Vp; dX = dXp; dV = dVp; ud = up; vd = vp;
     }
 }
 
@@ -356,8 +390,10 @@ struct HangingChain {
     static constexpr int MIN_BLOCKS = PANTR_MIN_BLOCKS;
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int) { return 0; }
-    // traj + dtraj + iwc
-    __host__ __device__ static int traj_doubles(int N) { return 2 * (N + 1) * NX + 4 * hc::NLINK * N; }
+    // traj + dtraj + iwc + adjc
+    __host__ __device__ static int traj_doubles(int N) {
+        return 2 * (N + 1) * NX + 4 * hc::NLINK * N + hc::SCSTEP * N;
+    }
     __host__ __device__ static double C_lb(int) { return -hc::v_max; } // hanging_chain.py:82-84
     __host__ __device__ static double C_ub(int) { return +hc::v_max; }
     __host__ __device__ static double D_lb(int, int) { return 0; }
@@ -370,15 +406,18 @@ struct HangingChain {
 
     int N;
     const double *x0;
-    double *traj, *dtraj, *iwc;
+    double *traj, *dtraj, *iwc, *adjc;
+    bool hvp_ready; // adjc holds the first-order stage data of the last rollout
 
     __device__ void init(int N_, const double *x0_, double *ws) {
         N = N_; x0 = x0_; traj = ws; dtraj = ws + (N_ + 1) * NX; iwc = ws + 2 * (N_ + 1) * NX;
+        adjc = iwc + 4 * hc::NLINK * N_; hvp_ready = false;
     }
     __device__ double eval_f(const double *u) { return eval_psi(u, nullptr, nullptr, nullptr); }
     __device__ void eval_g(const double *, double *) {}
     __device__ double eval_psi(const double *x, const double *, const double *, double *) {
         __syncwarp();
+        hvp_ready = false;
         double f = hc::rollout(N, x0, x, traj, iwc);
         __syncwarp();
         return f;
@@ -387,14 +426,16 @@ struct HangingChain {
         __syncwarp();
         double f = hc::rollout(N, x0, x, traj, iwc);
         __syncwarp();
-        hc::adjoint(N, x, traj, iwc, grad);
+        hc::adjoint(N, x, traj, iwc, grad, adjc);
+        hvp_ready = true;
         __syncwarp();
         return f;
     }
     /// Requires that the last rollout was at x (PANTR guarantees this: pantr.tpp:314 then :373).
     __device__ void hess_psi_prod(const double *x, const double *, const double *, const double *v, double *Hv) {
         __syncwarp();
-        hc::hvp(N, x, v, traj, dtraj, iwc, Hv);
+        if (!hvp_ready) (void)eval_psi_grad_psi(x, nullptr, nullptr, Hv); // Hv as scratch for the gradient
+        hc::hvp(N, x, v, traj, dtraj, iwc, adjc, Hv);
         __syncwarp();
     }
     /// Plant step x+ = f_d(x, u) (problems/problems/formulation.hpp:258-261)
