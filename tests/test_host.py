@@ -87,7 +87,7 @@ def test_enum_values_match_reference():
 
 def test_flop_model():
     F = flops.hanging_chain(60)
-    assert F["f"] == 1915 * 60 + 124 and F["psi_grad_psi"] == 5233 * 60 + 157 and F["hess_psi_prod"] == 11589 * 60 + 63
+    assert F["f"] == 1915 * 60 + 124 and F["psi_grad_psi"] == 3819 * 60 + 157 and F["hess_psi_prod"] == 8829 * 60 + 63
     st = np.zeros(3, dtype=pb.STATS_DTYPE)
     st["ev_psi"], st["ev_psi_grad_psi"], st["ev_grad_psi"], st["ev_hess_psi_prod"] = 2, 3, 1, 10
     assert flops.solve_flops("hanging_chain", 60, st) == 3 * (2 * F["f"] + 4 * F["psi_grad_psi"] + 10 * F["hess_psi_prod"])
