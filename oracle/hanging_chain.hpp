@@ -14,8 +14,10 @@
 // unpinned; tests check these sweeps against finite differences and a sympy derivation instead.
 #pragma once
 #include "oracle_core.hpp"
+#include "../pantr_cdc2023_experiments_b200/csrc/hc_formulas.h" // scalar formulas with explicit FMAs, shared with the CUDA path
 
 namespace oracle {
+namespace hcf = pantr::hcf;
 
 struct HangingChain : Problem {
     static constexpr int NL = 30, NVL = 27, NX = 57, NU = 3;
@@ -49,12 +51,12 @@ struct HangingChain : Problem {
         for (int i = 0; i < 10; ++i) {
             real_t n2 = (sq[3 * i] + sq[3 * i + 1]) + sq[3 * i + 2];
             real_t w = std::sqrt(n2), iw = 1.0 / w;
-            real_t c = Dspring * (1.0 - Lspring * iw), iw2 = iw * iw, e = (DL * iw) * iw2;
+            real_t c = hcf::spring_c(iw), iw2 = iw * iw, e = hcf::spring_e(iw, iw2);
             for (int d = 0; d < 3; ++d) { ld.c[3 * i + d] = c; ld.e[3 * i + d] = e; ld.iw2[3 * i + d] = iw2; }
         }
         for (int l = 0; l < NL; ++l) F[l] = ld.dist[l] * ld.c[l];
         for (int l = 0; l < NL; ++l) kX[l] = l < NVL ? V[l] : u[l - NVL];
-        for (int l = 0; l < NVL; ++l) kV[l] = (F[l + 3] - F[l]) * inv_m + grav(l % 3);
+        for (int l = 0; l < NVL; ++l) kV[l] = hcf::accel(F[l + 3], F[l], grav(l % 3));
     }
     static real_t dot3(const real_t *p, int l) { int b = l - l % 3; return (p[b] + p[b + 1]) + p[b + 2]; }
 
@@ -68,7 +70,7 @@ struct HangingChain : Problem {
         }
         for (int l = 0; l < NL; ++l) {
             real_t dt = dot3(pr, l);
-            db[l]     = ld.c[l] * Fbar[l] + (ld.e[l] * dt) * ld.dist[l];
+            db[l]     = hcf::force_lin(ld.c[l], Fbar[l], ld.e[l], dt, ld.dist[l]);
             if (dot_out) dot_out[l] = dt;
         }
         for (int l = 0; l < NL; ++l) aX[l] = l < NVL ? db[l] - db[l + 3] : db[l];
@@ -86,7 +88,7 @@ struct HangingChain : Problem {
         }
         for (int l = 0; l < NL; ++l) {
             dd[l] = dot3(pr, l);
-            dF[l] = ld.c[l] * ddist[l] + (ld.e[l] * dd[l]) * ld.dist[l];
+            dF[l] = hcf::force_lin(ld.c[l], ddist[l], ld.e[l], dd[l], ld.dist[l]);
         }
         for (int l = 0; l < NL; ++l) dkX[l] = l < NVL ? dV[l] : du[l - NVL];
         for (int l = 0; l < NVL; ++l) dkV[l] = (dF[l + 3] - dF[l]) * inv_m;
@@ -105,9 +107,8 @@ struct HangingChain : Problem {
             real_t df = dot3(p1, l), dot2 = dot3(p2, l);
             real_t dc = ld.e[l] * dd[l];
             real_t de = ((-3.0 * ld.e[l]) * ld.iw2[l]) * dd[l];
-            real_t lin = ld.c[l] * dFbar[l] + (ld.e[l] * dot2) * ld.dist[l];
-            real_t sec = (dc * Fbar[l] + (de * dotv[l] + ld.e[l] * df) * ld.dist[l]) +
-                         (ld.e[l] * dotv[l]) * ddist[l];
+            real_t lin = hcf::force_lin(ld.c[l], dFbar[l], ld.e[l], dot2, ld.dist[l]);
+            real_t sec = hcf::force_sec(dc, Fbar[l], de, dotv[l], ld.e[l], df, ld.dist[l], ddist[l]);
             ddb[l] = lin + sec;
         }
         for (int l = 0; l < NL; ++l) bX[l] = l < NVL ? ddb[l] - ddb[l + 3] : ddb[l];
@@ -118,8 +119,8 @@ struct HangingChain : Problem {
     // s2 = s + a*k (lane-wise)
     static void axpy_state(real_t a, const real_t *kX, const real_t *kV, const real_t *X,
                            const real_t *V, real_t *oX, real_t *oV) {
-        for (int l = 0; l < NL; ++l) oX[l] = X[l] + a * kX[l];
-        for (int l = 0; l < NVL; ++l) oV[l] = V[l] + a * kV[l];
+        for (int l = 0; l < NL; ++l) oX[l] = hcf::axpy(a, kX[l], X[l]);
+        for (int l = 0; l < NVL; ++l) oV[l] = hcf::axpy(a, kV[l], V[l]);
     }
 
     // One RK4 step of the plant / model: hanging_chain.py:58-66 ; also the driver's
@@ -134,9 +135,9 @@ struct HangingChain : Problem {
         axpy_state(hh, k2X, k2V, X, V, tX, tV); fc(tX, tV, u, k3X, k3V, ld);
         axpy_state(h, k3X, k3V, X, V, tX, tV);  fc(tX, tV, u, k4X, k4V, ld);
         for (int l = 0; l < NL; ++l)
-            sn[l] = X[l] + h6 * (((k1X[l] + 2.0 * k2X[l]) + 2.0 * k3X[l]) + k4X[l]);
+            sn[l] = hcf::rk4c(X[l], k1X[l], k2X[l], k3X[l], k4X[l]);
         for (int l = 0; l < NVL; ++l)
-            sn[NL + l] = V[l] + h6 * (((k1V[l] + 2.0 * k2V[l]) + 2.0 * k3V[l]) + k4V[l]);
+            sn[NL + l] = hcf::rk4c(V[l], k1V[l], k2V[l], k3V[l], k4V[l]);
     }
 
     // rollout + cost: ss.py:24-37
@@ -145,18 +146,18 @@ struct HangingChain : Problem {
         std::copy(x0.begin(), x0.end(), traj.begin());
         for (int k = 0; k < N; ++k) {
             const real_t *s = &traj[k * NX], *uk = u + NU * k;
-            for (int l = 0; l < NVL; ++l) acc[l] = acc[l] + beta * (s[NL + l] * s[NL + l]);
+            for (int l = 0; l < NVL; ++l) acc[l] = std::fma(beta, s[NL + l] * s[NL + l], acc[l]);
             for (int d = 0; d < 3; ++d) {
                 real_t dx = s[NVL + d] - ref(d);
-                acc[NVL + d] = acc[NVL + d] + (alpha * (dx * dx) + gamma_u * (uk[d] * uk[d]));
+                acc[NVL + d] = acc[NVL + d] + std::fma(alpha, dx * dx, gamma_u * (uk[d] * uk[d]));
             }
             rk4(s, uk, &traj[(k + 1) * NX]);
         }
         const real_t *s = &traj[N * NX];
-        for (int l = 0; l < NVL; ++l) acc[l] = acc[l] + beta * (s[NL + l] * s[NL + l]);
+        for (int l = 0; l < NVL; ++l) acc[l] = std::fma(beta, s[NL + l] * s[NL + l], acc[l]);
         for (int d = 0; d < 3; ++d) {
             real_t dx = s[NVL + d] - ref(d);
-            acc[NVL + d] = acc[NVL + d] + alpha * (dx * dx);
+            acc[NVL + d] = std::fma(alpha, dx * dx, acc[NVL + d]);
         }
         return butterfly_sum(acc);
     }

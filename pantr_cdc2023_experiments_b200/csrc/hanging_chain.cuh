@@ -25,6 +25,7 @@
 // SASS and stalled 14 of 19 cycles per issue on instruction fetch: profiles/r01_v0_*).
 #pragma once
 #include "warp_utils.cuh"
+#include "hc_formulas.h"
 
 namespace pantr {
 namespace hc {
@@ -66,11 +67,11 @@ __device__ __forceinline__ double fc(const Lane &L, double X, double Vu, double 
     double n2   = L.dot3(dist * dist);
     if (!L.active) n2 = 1.0;
     double w = sqrt(n2), iw = 1.0 / w;
-    double c  = Dspring * (1.0 - Lspring * iw);
+    double c  = hcf::spring_c(iw);
     double F  = dist * c;
     double Fu = shfl(F, L.l + 3);
     kX = Vu;
-    kV = (Fu - F) * inv_m + L.grav;
+    kV = hcf::accel(Fu, F, L.grav);
     return iw;
 }
 // the same stage evaluation from the cached iw (no sqrt, no division)
@@ -78,13 +79,13 @@ __device__ __forceinline__ void fc_cached(const Lane &L, double X, double Vu, do
                                           double &kV, Link &ld, double &iw2) {
     double Xm = shfl(X, L.l - 3);
     ld.dist   = L.l >= 3 ? X - Xm : X;
-    ld.c      = Dspring * (1.0 - Lspring * iw);
+    ld.c      = hcf::spring_c(iw);
     iw2       = iw * iw;
-    ld.e      = (DL * iw) * iw2;
+    ld.e      = hcf::spring_e(iw, iw2);
     double F  = ld.dist * ld.c;
     double Fu = shfl(F, L.l + 3);
     kX = Vu;
-    kV = (Fu - F) * inv_m + L.grav;
+    kV = hcf::accel(Fu, F, L.grav);
 }
 // (dfc/d(s,u))^T w ; aVu = adjoint of V (l<27) / of u (lanes 27..29)
 __device__ __forceinline__ void vjp(const Lane &L, const Link &ld, double wX, double wV, double &aX,
@@ -92,7 +93,7 @@ __device__ __forceinline__ void vjp(const Lane &L, const Link &ld, double wX, do
     double wVm = shfl(wV, L.l - 3);
     Fbar       = ((L.l >= 3 ? wVm : 0.0) - (L.hasV ? wV : 0.0)) * inv_m;
     dotv       = L.dot3(ld.dist * Fbar);
-    double db  = ld.c * Fbar + (ld.e * dotv) * ld.dist;
+    double db  = hcf::force_lin(ld.c, Fbar, ld.e, dotv, ld.dist);
     double dbu = shfl(db, L.l + 3);
     aX  = L.hasV ? db - dbu : db;
     aVu = wX;
@@ -103,7 +104,7 @@ __device__ __forceinline__ void jvp(const Lane &L, const Link &ld, double dX, do
     double dXm = shfl(dX, L.l - 3);
     ddist      = L.l >= 3 ? dX - dXm : dX;
     dd         = L.dot3(ld.dist * ddist);
-    double dF  = ld.c * ddist + (ld.e * dd) * ld.dist;
+    double dF  = hcf::force_lin(ld.c, ddist, ld.e, dd, ld.dist);
     double dFu = shfl(dF, L.l + 3);
     dkX = dVu;
     dkV = (dFu - dF) * inv_m;
@@ -118,8 +119,8 @@ __device__ __forceinline__ void hvjp(const Lane &L, const Link &ld, double iw2, 
     double dot2  = L.dot3(ld.dist * dFbar);
     double dc    = ld.e * dd;
     double de    = ((-3.0 * ld.e) * iw2) * dd;
-    double lin   = ld.c * dFbar + (ld.e * dot2) * ld.dist;
-    double sec   = (dc * Fbar + (de * dotv + ld.e * df) * ld.dist) + (ld.e * dotv) * ddist;
+    double lin   = hcf::force_lin(ld.c, dFbar, ld.e, dot2, ld.dist);
+    double sec   = hcf::force_sec(dc, Fbar, de, dotv, ld.e, df, ld.dist, ddist);
     double ddb   = lin + sec;
     double ddbu  = shfl(ddb, L.l + 3);
     bX  = L.hasV ? ddb - ddbu : ddb;
@@ -147,17 +148,17 @@ __device__ __forceinline__ void rk4(const Lane &L, double X, double V, double ud
     const bool wr = iw_out != nullptr && L.active && L.l == L.base;
     double iw = fc(L, X, L.hasV ? V : ud, k1X, k1V);
     if (wr) iw_out[L.link] = iw;
-    double tX = X + hh * k1X, tV = V + hh * k1V;
+    double tX = hcf::axpy(hh, k1X, X), tV = hcf::axpy(hh, k1V, V);
     iw = fc(L, tX, L.hasV ? tV : ud, k2X, k2V);
     if (wr) iw_out[NLINK + L.link] = iw;
-    tX = X + hh * k2X; tV = V + hh * k2V;
+    tX = hcf::axpy(hh, k2X, X); tV = hcf::axpy(hh, k2V, V);
     iw = fc(L, tX, L.hasV ? tV : ud, k3X, k3V);
     if (wr) iw_out[2 * NLINK + L.link] = iw;
-    tX = X + h * k3X; tV = V + h * k3V;
+    tX = hcf::axpy(h, k3X, X); tV = hcf::axpy(h, k3V, V);
     iw = fc(L, tX, L.hasV ? tV : ud, k4X, k4V);
     if (wr) iw_out[3 * NLINK + L.link] = iw;
-    Xn = X + h6 * (((k1X + 2.0 * k2X) + 2.0 * k3X) + k4X);
-    Vn = V + h6 * (((k1V + 2.0 * k2V) + 2.0 * k3V) + k4V);
+    Xn = hcf::rk4c(X, k1X, k2X, k3X, k4X);
+    Vn = hcf::rk4c(V, k1V, k2V, k3V, k4V);
 }
 
 // base stage link data of one RK4 step from the cached iw (X,V = s_k ; ud = u_k on lanes 27..29)
@@ -192,11 +193,11 @@ __device__ __forceinline__ void stages_cached(const Lane &L, double X, double V,
     double Vu = L.hasV ? V : ud, kX, kV;
     const double i0 = iw.i0, i1 = iw.i1, i2 = iw.i2, i3 = iw.i3;
     fc_cached(L, X, Vu, i0, kX, kV, ld[0], iw2[0]);
-    double tX = X + hh * kX, tV = V + hh * kV;
+    double tX = hcf::axpy(hh, kX, X), tV = hcf::axpy(hh, kV, V);
     fc_cached(L, tX, L.hasV ? tV : ud, i1, kX, kV, ld[1], iw2[1]);
-    tX = X + hh * kX; tV = V + hh * kV;
+    tX = hcf::axpy(hh, kX, X); tV = hcf::axpy(hh, kV, V);
     fc_cached(L, tX, L.hasV ? tV : ud, i2, kX, kV, ld[2], iw2[2]);
-    tX = X + h * kX; tV = V + h * kV;
+    tX = hcf::axpy(h, kX, X); tV = hcf::axpy(h, kV, V);
     fc_cached(L, tX, L.hasV ? tV : ud, i3, kX, kV, ld[3], iw2[3]);
 }
 
@@ -213,15 +214,15 @@ __device__ __noinline__ double rollout(int N, const double *x0, const double *u,
 #pragma unroll 1
     for (int k = 0; k < N; ++k) {
         double un = k + 1 < N ? load_u(L, u, k + 1) : 0.0;
-        if (L.hasV) acc = acc + beta * (V * V);
-        else if (L.isEnd) { double dx = X - L.ref; acc = acc + (alpha * (dx * dx) + gamma_u * (ud * ud)); }
+        if (L.hasV) acc = fma(beta, V * V, acc);
+        else if (L.isEnd) { double dx = X - L.ref; acc = acc + fma(alpha, dx * dx, gamma_u * (ud * ud)); }
         double Xn, Vn;
         rk4(L, X, V, ud, Xn, Vn, iwc + k * (4 * NLINK));
         X = Xn; V = Vn; ud = un;
         store_state(L, traj, k + 1, X, V);
     }
-    if (L.hasV) acc = acc + beta * (V * V);
-    else if (L.isEnd) { double dx = X - L.ref; acc = acc + alpha * (dx * dx); }
+    if (L.hasV) acc = fma(beta, V * V, acc);
+    else if (L.isEnd) { double dx = X - L.ref; acc = fma(alpha, dx * dx, acc); }
     __syncwarp();
     return warp_sum(acc);
 }
@@ -255,22 +256,22 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
         vjp(L, ld[3], wX, wV, aX, aV, Fb, dt);
         store_sc(L, ac + 3 * SC, Fb, dt);
         sX = lX + aX; sV = lV + aV;
-        wX = h3 * lX + h * aX; wV = h3 * lV + h * aV;
+        wX = hcf::lin2(h3, lX, h, aX); wV = hcf::lin2(h3, lV, h, aV);
         vjp(L, ld[2], wX, wV, aX, aV, Fb, dt);
         store_sc(L, ac + 2 * SC, Fb, dt);
         sX = sX + aX; sV = sV + aV;
-        wX = h3 * lX + hh * aX; wV = h3 * lV + hh * aV;
+        wX = hcf::lin2(h3, lX, hh, aX); wV = hcf::lin2(h3, lV, hh, aV);
         vjp(L, ld[1], wX, wV, aX, aV, Fb, dt);
         store_sc(L, ac + SC, Fb, dt);
         sX = sX + aX; sV = sV + aV;
-        wX = h6 * lX + hh * aX; wV = h6 * lV + hh * aV;
+        wX = hcf::lin2(h6, lX, hh, aX); wV = hcf::lin2(h6, lV, hh, aV);
         vjp(L, ld[0], wX, wV, aX, aV, Fb, dt);
         store_sc(L, ac, Fb, dt);
         sX = sX + aX; sV = sV + aV;
-        lX = L.isEnd ? sX + two_alpha * (X - L.ref) : sX;
-        if (L.hasV) lV = sV + two_beta * V;
+        lX = L.isEnd ? fma(two_alpha, X - L.ref, sX) : sX;
+        if (L.hasV) lV = fma(two_beta, V, sV);
         else {
-            if (L.isEnd) grad[NU * k + (L.l - NVL)] = sV + two_gamma * ud;
+            if (L.isEnd) grad[NU * k + (L.l - NVL)] = fma(two_gamma, ud, sV);
             lV = 0.0;
         }
         X = Xp; V = Vp; ud = up; iw = iwp;
@@ -302,14 +303,14 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
         stages_cached(L, X, V, ud, iw, ld, iw2);
         double k1X, k1V, k2X, k2V, k3X, k3V, k4X, k4V, ddist, dd;
         jvp(L, ld[0], dX, L.hasV ? dV : vd, k1X, k1V, ddist, dd);
-        double tX = dX + hh * k1X, tV = dV + hh * k1V;
+        double tX = hcf::axpy(hh, k1X, dX), tV = hcf::axpy(hh, k1V, dV);
         jvp(L, ld[1], tX, L.hasV ? tV : vd, k2X, k2V, ddist, dd);
-        tX = dX + hh * k2X; tV = dV + hh * k2V;
+        tX = hcf::axpy(hh, k2X, dX); tV = hcf::axpy(hh, k2V, dV);
         jvp(L, ld[2], tX, L.hasV ? tV : vd, k3X, k3V, ddist, dd);
-        tX = dX + h * k3X; tV = dV + h * k3V;
+        tX = hcf::axpy(h, k3X, dX); tV = hcf::axpy(h, k3V, dV);
         jvp(L, ld[3], tX, L.hasV ? tV : vd, k4X, k4V, ddist, dd);
-        dX = dX + h6 * (((k1X + 2.0 * k2X) + 2.0 * k3X) + k4X);
-        dV = dV + h6 * (((k1V + 2.0 * k2V) + 2.0 * k3V) + k4V);
+        dX = hcf::rk4c(dX, k1X, k2X, k3X, k4X);
+        dV = hcf::rk4c(dV, k1V, k2V, k3V, k4V);
         store_state(L, dtraj, k + 1, dX, dV);
         X = Xp; V = Vp; ud = up; vd = vp; iw = iwp;
     }
@@ -344,11 +345,11 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
         {
             double kX, kV;
             jvp(L, ld[0], dX, L.hasV ? dV : vd, kX, kV, ddist[0], dd[0]);
-            double sX = dX + hh * kX, sV = dV + hh * kV;
+            double sX = hcf::axpy(hh, kX, dX), sV = hcf::axpy(hh, kV, dV);
             jvp(L, ld[1], sX, L.hasV ? sV : vd, kX, kV, ddist[1], dd[1]);
-            sX = dX + hh * kX; sV = dV + hh * kV;
+            sX = hcf::axpy(hh, kX, dX); sV = hcf::axpy(hh, kV, dV);
             jvp(L, ld[2], sX, L.hasV ? sV : vd, kX, kV, ddist[2], dd[2]);
-            sX = dX + h * kX; sV = dV + h * kV;
+            sX = hcf::axpy(h, kX, dX); sV = hcf::axpy(h, kV, dV);
             jvp(L, ld[3], sX, L.hasV ? sV : vd, kX, kV, ddist[3], dd[3]);
         }
         double dwX, dwV, bX, bV, tX, tV;
@@ -357,22 +358,22 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
         hvjp(L, ld[3], iw2[3], Fb[3], dt[3], ddist[3], dd[3], dwX, dwV, bX, bV);
         tX = mX + bX; tV = mV + bV;
         // stage 3
-        dwX = h3 * mX + h * bX; dwV = h3 * mV + h * bV;
+        dwX = hcf::lin2(h3, mX, h, bX); dwV = hcf::lin2(h3, mV, h, bV);
         hvjp(L, ld[2], iw2[2], Fb[2], dt[2], ddist[2], dd[2], dwX, dwV, bX, bV);
         tX = tX + bX; tV = tV + bV;
         // stage 2
-        dwX = h3 * mX + hh * bX; dwV = h3 * mV + hh * bV;
+        dwX = hcf::lin2(h3, mX, hh, bX); dwV = hcf::lin2(h3, mV, hh, bV);
         hvjp(L, ld[1], iw2[1], Fb[1], dt[1], ddist[1], dd[1], dwX, dwV, bX, bV);
         tX = tX + bX; tV = tV + bV;
         // stage 1
-        dwX = h6 * mX + hh * bX; dwV = h6 * mV + hh * bV;
+        dwX = hcf::lin2(h6, mX, hh, bX); dwV = hcf::lin2(h6, mV, hh, bV);
         hvjp(L, ld[0], iw2[0], Fb[0], dt[0], ddist[0], dd[0], dwX, dwV, bX, bV);
         tX = tX + bX; tV = tV + bV;
         // stage cost
-        mX = L.isEnd ? tX + two_alpha * dX : tX;
-        if (L.hasV) mV = tV + two_beta * dV;
+        mX = L.isEnd ? fma(two_alpha, dX, tX) : tX;
+        if (L.hasV) mV = fma(two_beta, dV, tV);
         else {
-            if (L.isEnd) Hv[NU * k + (L.l - NVL)] = tV + two_gamma * vd;
+            if (L.isEnd) Hv[NU * k + (L.l - NVL)] = fma(two_gamma, vd, tV);
             mV = 0.0;
         }
         X = Xp; V = Vp; dX = dXp; dV = dVp; ud = up; vd = vp;
