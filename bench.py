@@ -351,9 +351,17 @@ def run_b200(args):
     state_bytes = B * ((nx + 2 * n) * 8 + pb.STATS_DTYPE.itemsize)
     peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
     hbm_peak = json.load(open(peaks_file))["hbm_gbs"] if os.path.exists(peaks_file) else 6650.0
+    # DRAM traffic of this launch shape from the committed `ncu --set full` capture (never measured live)
+    traffic, traffic_src = None, None
+    tfile = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tfile):
+        tj = json.load(open(tfile))
+        if tj.get("batch") == B and tj.get("horizon") == N:
+            traffic, traffic_src = tj["dram_bytes_per_launch"], tj.get("source")
     roofline = {
         "bound": "fp64", "achieved": achieved, "peak": peak.value, "unit": "TFLOP/s",
-        "frac": achieved / peak.value if peak.value > 0 else None, "traffic": None,
+        "frac": achieved / peak.value if peak.value > 0 else None, "traffic": traffic,
+        "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_source": traffic_src,
         "kernel": "solve_kernel<HangingChain>", "kernel_ms": kernel_ms,
         "flops_per_launch": F_local, "flops_per_solve": F_local / B,
         "peak_source": "FP64 DFMA peak measured live on this GPU (pantr_b200_measure_fp64_peak); "

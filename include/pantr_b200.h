@@ -148,6 +148,59 @@ int pantr_b200_eval_batch(pantr_b200_solver *s, int64_t B, const double *x0, con
                           const double *y, const double *Sigma, const double *v, double *psi,
                           double *grad, double *yhat, double *Hv);
 
+/* ---- Problem plugin face: the members of alpaqa_problem_functions_t
+ * (alpaqa/src/interop/dl-api/include/alpaqa/dl/dl-problem.h:13-153) evaluated for B instances per call,
+ * HOST buffers, instance-major ([B*n], [B*m]).  x0 [B*nx] is the NLP parameter (the initial state,
+ * CasADiProblem::param); the model comes from the handle.  Semantics: CasADiProblem::eval_*
+ * (alpaqa/src/interop/casadi/include/alpaqa/implementation/casadi/CasADiProblem.tpp:208-368) for the
+ * smooth functions, BoxConstrProblem (alpaqa/problem/box-constr-problem.hpp:59-185) for the box ones.
+ * With m == 0 the m-sized arguments may be NULL and eval_g / eval_proj_* are no-ops. ---- */
+/* dl-problem.h:18-20 eval_f */
+int pantr_b200_eval_f_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x, double *f);
+/* dl-problem.h:21-24 eval_grad_f */
+int pantr_b200_eval_grad_f_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x,
+                                 double *grad_fx);
+/* dl-problem.h:87-90 eval_f_grad_f */
+int pantr_b200_eval_f_grad_f_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x,
+                                   double *f, double *grad_fx);
+/* dl-problem.h:25-28 eval_g : gx [B*m] */
+int pantr_b200_eval_g_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x, double *gx);
+/* dl-problem.h:29-33 eval_grad_g_prod : J_g(x)' y */
+int pantr_b200_eval_grad_g_prod_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x,
+                                      const double *y, double *grad_gxy);
+/* dl-problem.h:101-106 eval_grad_L : grad f + J_g' y */
+int pantr_b200_eval_grad_L_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x,
+                                 const double *y, double *grad_L);
+/* dl-problem.h:47-53 eval_hess_L_prod : scale * hess_xx L(x, y) v */
+int pantr_b200_eval_hess_L_prod_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x,
+                                      const double *y, double scale, const double *v, double *Hv);
+/* dl-problem.h:64-73 eval_hess_psi_prod : scale * hess_xx psi(x; y, Sigma) v  (D = the model's box) */
+int pantr_b200_eval_hess_psi_prod_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x,
+                                        const double *y, const double *Sigma, double scale, const double *v,
+                                        double *Hv);
+/* dl-problem.h:107-114 eval_psi : psi [B], yhat [B*m] (may be NULL) */
+int pantr_b200_eval_psi_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x,
+                              const double *y, const double *Sigma, double *yhat, double *psi);
+/* dl-problem.h:115-124 eval_grad_psi */
+int pantr_b200_eval_grad_psi_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x,
+                                   const double *y, const double *Sigma, double *grad_psi);
+/* dl-problem.h:125-134 eval_psi_grad_psi */
+int pantr_b200_eval_psi_grad_psi_batch(pantr_b200_solver *s, int64_t B, const double *x0, const double *x,
+                                       const double *y, const double *Sigma, double *psi, double *grad_psi);
+/* dl-problem.h:135-141, box-constr-problem.hpp:59-64,107-114 eval_prox_grad_step : p = clamp(-gamma grad_psi, C - x), x_hat = x + p
+ * (h = 0: the benchmark problems have no l1 term) */
+int pantr_b200_eval_prox_grad_step_batch(pantr_b200_solver *s, int64_t B, double gamma, const double *x,
+                                         const double *grad_psi, double *x_hat, double *p);
+/* box-constr-problem.hpp:117 eval_proj_diff_g : e = z - Pi_D(z) */
+int pantr_b200_eval_proj_diff_g_batch(pantr_b200_solver *s, int64_t B, const double *z, double *e);
+/* box-constr-problem.hpp:119-143 eval_proj_multipliers : y clamped in place to [-M or 0, +M or 0] */
+int pantr_b200_eval_proj_multipliers_batch(pantr_b200_solver *s, int64_t B, double *y, double M);
+/* box-constr-problem.hpp:151-185 eval_inactive_indices_res_lna : J [B*n] (first nJ[b] entries of row b,
+ * ascending), nJ [B] */
+int pantr_b200_eval_inactive_indices_res_lna_batch(pantr_b200_solver *s, int64_t B, double gamma,
+                                                   const double *x, const double *grad_psi, int32_t *J,
+                                                   int32_t *nJ);
+
 /* Plant step x+ = f_d(x, u) for B instances ("simulate_dynamics" extra function,
  * problems/problems/formulation.hpp:258-261), HOST buffers: x [B*nx], u [B*nu] -> xn [B*nx]. */
 int pantr_b200_simulate_dynamics_batch(pantr_b200_solver *s, int64_t B, const double *x,

@@ -108,6 +108,44 @@ int oracle_eval(int problem_id, int N, const double *x0, const double *u, const 
     return 0;
 }
 
+// One member of the problem plugin table (fn = pantr::ProblemFn of csrc/problem_face.cuh) for one instance.
+// v doubles as grad_psi for the box functions, y as z; scalar = scale / gamma / M.
+int oracle_problem_eval(int problem_id, int N, int fn, const double *x0, const double *x, const double *y,
+                        const double *Sigma, const double *v, double scalar, double *out_s, double *out_n,
+                        double *out_n2, double *out_m, int *out_i, int *out_cnt) {
+    auto p = make_problem(problem_id, N);
+    if (!p) return -1;
+    if (x0) set_x0(*p, problem_id, x0);
+    switch (fn) {
+        case 0: *out_s = p->eval_f(x); break;
+        case 1: (void)p->face_grad_L(x, nullptr, out_n); break;
+        case 2: *out_s = p->face_grad_L(x, nullptr, out_n); break;
+        case 3: p->eval_g(x, out_m); break;
+        case 4: p->face_grad_g_prod(x, y, out_n); break;
+        case 5: (void)p->face_grad_L(x, y, out_n); break;
+        case 6: p->face_hess_L_prod(x, y, scalar, v, out_n); break;
+        case 7:
+            p->eval_hess_psi_prod(x, y, Sigma, scalar, v, out_n);
+            if (scalar != 1 && problem_id != 0) for (index_t i = 0; i < p->n; ++i) out_n[i] *= scalar;
+            break;
+        case 8: (void)p->eval_prox_grad_step(scalar, x, v, out_n, out_n2); break;
+        case 9: p->eval_proj_diff_g(y, out_m); break;
+        case 10:
+            for (index_t i = 0; i < p->m; ++i) out_m[i] = y[i];
+            p->eval_proj_multipliers(out_m, scalar);
+            break;
+        case 11: {
+            std::vector<index_t> J(p->n);
+            index_t nJ = p->eval_inactive_indices_res_lna(scalar, x, v, J.data());
+            for (index_t j = 0; j < nJ; ++j) out_i[j] = (int)J[j];
+            *out_cnt = (int)nJ;
+            break;
+        }
+        default: return -1;
+    }
+    return 0;
+}
+
 // Plant step x+ = f_d(x, u): problems/problems/formulation.hpp:258-261
 int oracle_simulate_dynamics(int problem_id, const double *x, const double *u, double *xn) {
     if (problem_id == 0) { HangingChain hc(1); hc.rk4(x, u, xn); return 0; }

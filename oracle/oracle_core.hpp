@@ -107,6 +107,13 @@ struct Problem {
                                          const real_t *S, real_t scale,
                                          const real_t *v, real_t *Hv) const   = 0;
 
+    // -- problem plugin face beyond what PANTR calls (CasADiProblem.tpp:226-233,268-276,300-313):
+    //    J_g' y, grad L = grad f + J_g' y (returns f), hess_xx L v --
+    //    (only the MPC models implement them; the KAT problems do not need them)
+    virtual void face_grad_g_prod(const real_t *, const real_t *, real_t *) const {}
+    virtual real_t face_grad_L(const real_t *, const real_t *, real_t *) const { return 0; }
+    virtual void face_hess_L_prod(const real_t *, const real_t *, real_t, const real_t *, real_t *) const {}
+
     // -- counted wrappers: problem/problem-with-counters.hpp:24-112 --
     real_t eval_f(const real_t *x) const { ++evaluations.f; return eval_f_impl(x); }
     void eval_g(const real_t *x, real_t *g) const { ++evaluations.g; eval_g_impl(x, g); }

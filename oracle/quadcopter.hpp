@@ -68,6 +68,26 @@ struct Quadcopter : Problem {
         if (!hvp_ready) (void)eval_psi_grad_psi_impl(x, y, S, Hv);
         pantr::quad::hvp<G>(N, x, v, w, Hv);
     }
+    // ---- problem plugin face ----
+    void set_multipliers(const real_t *y) const {
+        for (index_t i = 0; i < m; ++i) { w.yh[i] = y ? y[i] : 0.0; w.wact[i] = 0.0; }
+    }
+    real_t face_grad_L(const real_t *x, const real_t *y, real_t *grad) const override {
+        real_t f = eval_f_impl(x);
+        set_multipliers(y);
+        pantr::quad::adjoint<G>(N, x, w, grad);
+        return f;
+    }
+    void face_grad_g_prod(const real_t *x, const real_t *y, real_t *out) const override {
+        (void)eval_f_impl(x);
+        set_multipliers(y);
+        pantr::quad::adjoint<G, false>(N, x, w, out);
+    }
+    void face_hess_L_prod(const real_t *x, const real_t *y, real_t scale, const real_t *v, real_t *Hv) const override {
+        (void)face_grad_L(x, y, Hv);
+        pantr::quad::hvp<G>(N, x, v, w, Hv);
+        if (scale != 1) for (index_t i = 0; i < n; ++i) Hv[i] *= scale;
+    }
 };
 
 using SimpleQuadcopter    = Quadcopter<pantr::quad::SimpleGen>;

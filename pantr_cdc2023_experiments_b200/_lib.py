@@ -67,6 +67,13 @@ SYMBOLS = [
     "pantr_b200_shift_warm_start_device", "pantr_b200_set_trace", "pantr_b200_get_trace",
     "pantr_b200_kernel_launches", "pantr_b200_grid_size", "pantr_b200_measure_fp64_peak",
     "pantr_b200_last_error",
+    # problem plugin face (alpaqa_problem_functions_t members, batched)
+    "pantr_b200_eval_f_batch", "pantr_b200_eval_grad_f_batch", "pantr_b200_eval_f_grad_f_batch",
+    "pantr_b200_eval_g_batch", "pantr_b200_eval_grad_g_prod_batch", "pantr_b200_eval_grad_L_batch",
+    "pantr_b200_eval_hess_L_prod_batch", "pantr_b200_eval_hess_psi_prod_batch", "pantr_b200_eval_psi_batch",
+    "pantr_b200_eval_grad_psi_batch", "pantr_b200_eval_psi_grad_psi_batch",
+    "pantr_b200_eval_prox_grad_step_batch", "pantr_b200_eval_proj_diff_g_batch",
+    "pantr_b200_eval_proj_multipliers_batch", "pantr_b200_eval_inactive_indices_res_lna_batch",
 ]
 
 _lib = None
@@ -109,6 +116,22 @@ def load():
     lib.pantr_b200_kernel_launches.restype = i64
     lib.pantr_b200_grid_size.argtypes = [vp]
     lib.pantr_b200_measure_fp64_peak.argtypes = [C.c_int, C.c_int, dp]
+    f64 = C.c_double
+    lib.pantr_b200_eval_f_batch.argtypes = [vp, i64, vp, vp, vp]
+    lib.pantr_b200_eval_grad_f_batch.argtypes = [vp, i64, vp, vp, vp]
+    lib.pantr_b200_eval_f_grad_f_batch.argtypes = [vp, i64, vp, vp, vp, vp]
+    lib.pantr_b200_eval_g_batch.argtypes = [vp, i64, vp, vp, vp]
+    lib.pantr_b200_eval_grad_g_prod_batch.argtypes = [vp, i64, vp, vp, vp, vp]
+    lib.pantr_b200_eval_grad_L_batch.argtypes = [vp, i64, vp, vp, vp, vp]
+    lib.pantr_b200_eval_hess_L_prod_batch.argtypes = [vp, i64, vp, vp, vp, f64, vp, vp]
+    lib.pantr_b200_eval_hess_psi_prod_batch.argtypes = [vp, i64, vp, vp, vp, vp, f64, vp, vp]
+    lib.pantr_b200_eval_psi_batch.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp]
+    lib.pantr_b200_eval_grad_psi_batch.argtypes = [vp, i64, vp, vp, vp, vp, vp]
+    lib.pantr_b200_eval_psi_grad_psi_batch.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp]
+    lib.pantr_b200_eval_prox_grad_step_batch.argtypes = [vp, i64, f64, vp, vp, vp, vp]
+    lib.pantr_b200_eval_proj_diff_g_batch.argtypes = [vp, i64, vp, vp]
+    lib.pantr_b200_eval_proj_multipliers_batch.argtypes = [vp, i64, vp, f64]
+    lib.pantr_b200_eval_inactive_indices_res_lna_batch.argtypes = [vp, i64, f64, vp, vp, vp, vp]
     _lib = lib
     return lib
 

@@ -129,13 +129,13 @@ __device__ __forceinline__ void hvjp(const Lane &L, const Link &ld, double iw2, 
 
 __device__ __forceinline__ void load_state(const Lane &L, const double *t, int k, double &X, double &V) {
     const double *s = t + k * NX;
-    X = L.active ? s[L.l] : 0.0;
-    V = L.hasV ? s[NL + L.l] : 0.0;
+    X = L.active ? __ldcg(s + L.l) : 0.0; // streamed once per sweep: L2 only, L1 stays with the solver vectors
+    V = L.hasV ? __ldcg(s + NL + L.l) : 0.0;
 }
 __device__ __forceinline__ void store_state(const Lane &L, double *t, int k, double X, double V) {
     double *s = t + k * NX;
-    if (L.active) s[L.l] = X;
-    if (L.hasV) s[NL + L.l] = V;
+    if (L.active) __stcg(s + L.l, X);
+    if (L.hasV) __stcg(s + NL + L.l, V);
 }
 __device__ __forceinline__ double load_u(const Lane &L, const double *u, int k) {
     return L.isEnd ? u[NU * k + (L.l - NVL)] : 0.0;
@@ -147,16 +147,16 @@ __device__ __forceinline__ void rk4(const Lane &L, double X, double V, double ud
     double k1X, k1V, k2X, k2V, k3X, k3V, k4X, k4V;
     const bool wr = iw_out != nullptr && L.active && L.l == L.base;
     double iw = fc(L, X, L.hasV ? V : ud, k1X, k1V);
-    if (wr) iw_out[L.link] = iw;
+    if (wr) __stcg(iw_out + L.link, iw);
     double tX = hcf::axpy(hh, k1X, X), tV = hcf::axpy(hh, k1V, V);
     iw = fc(L, tX, L.hasV ? tV : ud, k2X, k2V);
-    if (wr) iw_out[NLINK + L.link] = iw;
+    if (wr) __stcg(iw_out + NLINK + L.link, iw);
     tX = hcf::axpy(hh, k2X, X); tV = hcf::axpy(hh, k2V, V);
     iw = fc(L, tX, L.hasV ? tV : ud, k3X, k3V);
-    if (wr) iw_out[2 * NLINK + L.link] = iw;
+    if (wr) __stcg(iw_out + 2 * NLINK + L.link, iw);
     tX = hcf::axpy(h, k3X, X); tV = hcf::axpy(h, k3V, V);
     iw = fc(L, tX, L.hasV ? tV : ud, k4X, k4V);
-    if (wr) iw_out[3 * NLINK + L.link] = iw;
+    if (wr) __stcg(iw_out + 3 * NLINK + L.link, iw);
     Xn = hcf::rk4c(X, k1X, k2X, k3X, k4X);
     Vn = hcf::rk4c(V, k1V, k2V, k3V, k4V);
 }
@@ -165,28 +165,37 @@ __device__ __forceinline__ void rk4(const Lane &L, double X, double V, double ud
 struct IW { double i0, i1, i2, i3; };
 __device__ __forceinline__ IW load_iw(const Lane &L, const double *iwc, int k) {
     const double *p = iwc + k * (4 * NLINK) + L.link;
-    return IW{p[0], p[NLINK], p[2 * NLINK], p[3 * NLINK]};
-}
-__device__ __forceinline__ void prefetch_iw(const Lane &L, const double *iwc, int k) {
-    if (L.l < 4) {
-        const double *p = iwc + k * (4 * NLINK) + (L.l < 3 ? 16 * L.l : 4 * NLINK - 1);
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
-    }
+    return IW{__ldcg(p), __ldcg(p + NLINK), __ldcg(p + 2 * NLINK), __ldcg(p + 3 * NLINK)};
 }
 // Per-stage caches, 40 doubles per stage point (4 per RK4 step): entries 0..29 are lane values,
 // 30..39 the per-link scalars (written by the link's base lane).
 constexpr int SC = NL + NLINK, SCSTEP = 4 * SC;
 __device__ __forceinline__ void store_sc(const Lane &L, double *c, double lanev, double linkv) {
-    if (L.active) c[L.l] = lanev;
-    if (L.active && L.l == L.base) c[NL + L.link] = linkv;
+    if (L.active) __stcg(c + L.l, lanev);
+    if (L.active && L.l == L.base) __stcg(c + NL + L.link, linkv);
 }
 __device__ __forceinline__ void load_sc(const Lane &L, const double *c, double &lanev, double &linkv) {
     lanev = L.active ? c[L.l] : 0.0;
     linkv = c[NL + L.link];
 }
-/// pulls the 10 cache lines of one step's block (160 doubles) into L1
-__device__ __forceinline__ void prefetch_sc(const Lane &L, const double *c) {
-    if (L.l < 10) asm volatile("prefetch.global.L1 [%0];" ::"l"(c + 16 * L.l));
+// ---- shared-memory staging of the reverse sweep's per-step cache block (adjc: 160 doubles, iwc: 40) ----
+// cp.async (LDGSTS, L2 -> shared, bypassing L1) fetches step k-1 while step k computes; the
+// L1-prefetch version still stalled ~1300 cycles per step on the first use of iw / Fbar
+// (profiles/r01_v7_*: 10 % of all warp samples on one DFMA).
+constexpr int STAGE_D = SCSTEP + 4 * NLINK; // 200 doubles
+__device__ __forceinline__ void cp_async16(double *smem, const double *g) {
+    unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void stage_fetch(const Lane &L, double *buf, const double *ac, const double *iw) {
+    const int l = lane_id();
+    cp_async16(buf + 2 * l, ac + 2 * l);
+    cp_async16(buf + 2 * (l + 32), ac + 2 * (l + 32));
+    if (l < 16) cp_async16(buf + 2 * (l + 64), ac + 2 * (l + 64));
+    if (l < 20) cp_async16(buf + SCSTEP + 2 * l, iw + 2 * l);
+    (void)L;
 }
 __device__ __forceinline__ void stages_cached(const Lane &L, double X, double V, double ud, const IW &iw,
                                               Link (&ld)[4], double (&iw2)[4]) {
@@ -233,7 +242,7 @@ __device__ __noinline__ double rollout(int N, const double *x0, const double *u,
 __device__ __noinline__ void adjoint(int N, const double *u, const double *traj, const double *iwc,
                                      double *grad, double *adjc) {
     __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(traj)); __builtin_assume(__isGlobal(iwc));
-    __builtin_assume(__isGlobal(grad)); __builtin_assume(__isGlobal(adjc));
+    __builtin_assume(__isGlobal(adjc)); // grad may be shared memory
     const Lane L;
     double X, V, lX, lV;
     load_state(L, traj, N, X, V);
@@ -283,8 +292,8 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
 // traj / iwc hold the rollout of `u`; dtraj is scratch for the tangent trajectory.
 __device__ __noinline__ void hvp(int N, const double *u, const double *v, const double *traj, double *dtraj,
                                  const double *iwc, const double *adjc, double *Hv) {
-    __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(v)); __builtin_assume(__isGlobal(traj));
-    __builtin_assume(__isGlobal(dtraj)); __builtin_assume(__isGlobal(iwc)); __builtin_assume(__isGlobal(Hv));
+    __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(traj)); // v, Hv may be shared memory
+    __builtin_assume(__isGlobal(dtraj)); __builtin_assume(__isGlobal(iwc));
     __builtin_assume(__isGlobal(adjc));
     const Lane L;
     double X, V, dX = 0.0, dV = 0.0;
@@ -326,19 +335,28 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
     load_state(L, traj, N - 1, X, V);
     load_state(L, dtraj, N - 1, dX, dV);
     ud = load_u(L, u, N - 1); vd = load_u(L, v, N - 1);
+    __shared__ __align__(16) double stage[2][STAGE_D];
+    __syncwarp();
+    stage_fetch(L, stage[0], adjc + (N - 1) * SCSTEP, iwc + (N - 1) * (4 * NLINK));
+    cp_async_commit();
+    int cur = 0;
 #pragma unroll 1
     for (int k = N - 1; k >= 0; --k) {
-        const double *ac = adjc + k * SCSTEP;
+        cp_async_wait_all();
+        __syncwarp();
+        const double *sb = stage[cur];
+        if (k > 0) stage_fetch(L, stage[cur ^ 1], adjc + (k - 1) * SCSTEP, iwc + (k - 1) * (4 * NLINK));
+        cp_async_commit();
+        cur ^= 1;
         double Fb[4], dt[4], ddist[4], dd[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) load_sc(L, ac + j * SC, Fb[j], dt[j]);
-        const IW iw = load_iw(L, iwc, k);
+        for (int j = 0; j < 4; ++j) { Fb[j] = L.active ? sb[j * SC + L.l] : 0.0; dt[j] = sb[j * SC + NL + L.link]; }
+        const IW iw{sb[SCSTEP + L.link], sb[SCSTEP + NLINK + L.link], sb[SCSTEP + 2 * NLINK + L.link],
+                    sb[SCSTEP + 3 * NLINK + L.link]};
         double Xp = 0, Vp = 0, dXp = 0, dVp = 0, up = 0, vp = 0;
         if (k > 0) {
             load_state(L, traj, k - 1, Xp, Vp); load_state(L, dtraj, k - 1, dXp, dVp);
             up = load_u(L, u, k - 1); vp = load_u(L, v, k - 1);
-            prefetch_iw(L, iwc, k - 1);
-            prefetch_sc(L, ac - SCSTEP);
         }
         Link ld[4]; double iw2[4];
         stages_cached(L, X, V, ud, iw, ld, iw2);
@@ -438,6 +456,18 @@ struct HangingChain {
         if (!hvp_ready) (void)eval_psi_grad_psi(x, nullptr, nullptr, Hv); // Hv as scratch for the gradient
         hc::hvp(N, x, v, traj, dtraj, iwc, adjc, Hv);
         __syncwarp();
+    }
+    // ---- problem plugin face (m = 0: L = f) ----
+    __device__ double eval_grad_L(const double *x, const double *, double *grad) {
+        return eval_psi_grad_psi(x, nullptr, nullptr, grad);
+    }
+    __device__ void eval_grad_g_prod(const double *, const double *, double *out) {
+        for (int i = lane_id(); i < n(N); i += 32) out[i] = 0.0;
+        __syncwarp();
+    }
+    __device__ void hess_L_prod(const double *x, const double *, const double *v, double *Hv) {
+        hvp_ready = false;
+        hess_psi_prod(x, nullptr, nullptr, v, Hv);
     }
     /// Plant step x+ = f_d(x, u) (problems/problems/formulation.hpp:258-261)
     __device__ static void plant_step(const double *x, const double *u, double *xn) {

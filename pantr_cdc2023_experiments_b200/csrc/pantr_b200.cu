@@ -4,6 +4,7 @@
 #include "pantr_device.cuh"
 #include "hanging_chain.cuh"
 #include "quadcopter.cuh"
+#include "problem_face.cuh"
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -32,6 +33,7 @@ struct KernelArgs {
     size_t ws_stride; // doubles per block
     unsigned long long *counter;
     Trace trace;
+    int smem_set; // which solver vectors live in dynamic shared memory (Pantr::smem_bytes)
 };
 
 // ---- the solve kernel: ALMSolver::operator() for every instance of the batch ----
@@ -39,6 +41,7 @@ template <class Model>
 __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __grid_constant__ SolverParams P,
                                                    const __grid_constant__ KernelArgs A) {
     __shared__ IterScalars it[3];
+    extern __shared__ __align__(16) double dyn_smem[];
     double *ws = A.ws + size_t(blockIdx.x) * A.ws_stride;
     for (;;) {
         unsigned long long b = 0;
@@ -48,7 +51,7 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
         long long t0 = clock64();
         Model mdl;
         mdl.init(A.N, A.x0 + b * A.nx, ws);
-        Pantr<Model> S(mdl, P, it, A.n, A.m, ws + Model::traj_doubles(A.N));
+        Pantr<Model> S(mdl, P, it, A.n, A.m, ws + Model::traj_doubles(A.N), dyn_smem, A.smem_set);
         memset(&S.st, 0, sizeof(S.st));
         S.x = A.u + b * A.n;
         for (int i = lane_id(); i < A.m; i += 32) S.y[i] = A.y[b * A.m + i];
@@ -142,3 +145,4 @@ __global__ void __launch_bounds__(256) fp64_peak_kernel(double *out, int iters, 
 } // namespace
 
 #include "pantr_b200_host.inc"
+#include "pantr_b200_problem.inc"

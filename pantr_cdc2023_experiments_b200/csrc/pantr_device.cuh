@@ -42,7 +42,13 @@ struct Pantr {
     bool tracing;
     Trace tr;
 
-    __device__ Pantr(Model &mdl_, const SolverParams &P_, IterScalars *it_, int n_, int m_, double *ws)
+    /// sm / smem_set: the Steihaug-CG vectors (set >= 1: z, r, d, Bd; set 2: also work, work2 and the
+    /// J/K index list) live in the block's shared memory instead of the global workspace.
+    __host__ __device__ static size_t smem_bytes(int n, int set) {
+        return set == 0 ? 0 : (set == 1 ? size_t(4) * n * 8 : size_t(6) * n * 8 + size_t(n + 2) / 2 * 8);
+    }
+    __device__ Pantr(Model &mdl_, const SolverParams &P_, IterScalars *it_, int n_, int m_, double *ws,
+                     double *sm = nullptr, int smem_set = 0)
         : mdl(mdl_), P(P_), it(it_), n(n_), m(m_) {
         double *p = ws;
         X = p; p += 3 * n; XH = p; p += 3 * n; G = p; p += 3 * n; PP = p; p += 3 * n;
@@ -53,6 +59,8 @@ struct Pantr {
         y = p; p += m; Sig = p; p += m; Sig_old = p; p += m; e1 = p; p += m; e2 = p; p += m;
         p += 2 * m; // spare (10 m-vectors)
         JK = reinterpret_cast<int *>(p);
+        if (smem_set >= 1) { z = sm; r = sm + n; d = sm + 2 * n; Bd = sm + 3 * n; }
+        if (smem_set >= 2) { work = sm + 4 * n; work2 = sm + 5 * n; JK = reinterpret_cast<int *>(sm + 6 * n); }
     }
     __host__ __device__ static size_t ws_doubles(int n, int m) {
         return size_t(WS_NVEC) * n + size_t(WS_MVEC) * m + (n + 1) / 2 + 2;

@@ -68,6 +68,35 @@ struct QuadcopterModel {
         quad::hvp<G>(N, x, v, w, Hv);
         __syncwarp();
     }
+    // ---- problem plugin face (alpaqa_problem_functions_t members that PANTR itself does not call) ----
+    /// y_hat := y (zero if null), no active quadratic penalty: the adjoint / hvp sweeps then give grad L / hess L
+    __device__ void set_multipliers(const double *y) {
+        const int mm = m(N);
+        for (int i = 0; i < mm; ++i) { w.yh[i] = y ? y[i] : 0.0; w.wact[i] = 0.0; }
+    }
+    /// grad L(x, y) = grad f + J_g' y (CasADiProblem::eval_grad_L, CasADiProblem.tpp:268-276); returns f
+    __device__ __noinline__ double eval_grad_L(const double *x, const double *y, double *grad) {
+        double f = eval_f(x);
+        set_multipliers(y);
+        quad::adjoint<G>(N, x, w, grad);
+        hvp_ready = false; // w.yh no longer holds the y_hat of a psi_grad_psi
+        __syncwarp();
+        return f;
+    }
+    /// J_g(x)' y (CasADiProblem::eval_grad_g_prod, CasADiProblem.tpp:226-233)
+    __device__ __noinline__ void eval_grad_g_prod(const double *x, const double *y, double *out) {
+        (void)eval_f(x);
+        set_multipliers(y);
+        quad::adjoint<G, false>(N, x, w, out);
+        __syncwarp();
+    }
+    /// hess_xx L(x, y) v (CasADiProblem::eval_hess_L_prod, CasADiProblem.tpp:300-313); Hv is also scratch
+    __device__ __noinline__ void hess_L_prod(const double *x, const double *y, const double *v, double *Hv) {
+        (void)eval_grad_L(x, y, Hv);
+        quad::hvp<G>(N, x, v, w, Hv);
+        hvp_ready = false;
+        __syncwarp();
+    }
     /// Plant step x+ = f_d(x, u) (problems/problems/formulation.hpp:258-261)
     __device__ static void plant_step(const double *x, const double *u, double *xn) {
         double xx[NX], uu[NU], o[NX];

@@ -184,13 +184,14 @@ PANTR_HD double al_terms(int N, const QuadWS &w, const double *y, const double *
 
 /// grad psi = grad f + J_g' y_hat by discrete adjoint; needs the rollout of u and w.yh.  Stores
 /// the adjoint stage weights in w.wst.
-template <class G>
+/// COST = false drops the cost terms: grad = J_g' y_hat (eval_grad_g_prod of the problem plugin face).
+template <class G, bool COST = true>
 PANTR_HD void adjoint(int N, const double *u, const QuadWS &w, double *grad) {
     double lam[NX], ax[NX], au[NU], s[NX], su[NU], wt[NX], uk[NU];
     {
         const double *x = w.traj + NX * N;
         G::con_vjp(x, w.sc + 24 * N, w.yh + NC * N, ax);
-        PANTR_UNROLL for (int i = 0; i < NX; ++i) lam[i] = dcost_x(x, i, true) + ax[i];
+        PANTR_UNROLL for (int i = 0; i < NX; ++i) lam[i] = COST ? dcost_x(x, i, true) + ax[i] : ax[i];
     }
     PANTR_NOUNROLL
     for (int k = N - 1; k >= 0; --k) {
@@ -217,10 +218,10 @@ PANTR_HD void adjoint(int N, const double *u, const QuadWS &w, double *grad) {
         G::fc_vjp(x, uk, sc, wt, ax, au);
         PANTR_UNROLL for (int i = 0; i < NX; ++i) s[i] = s[i] + ax[i];
         PANTR_UNROLL for (int j = 0; j < NU; ++j) su[j] = su[j] + au[j];
-        PANTR_UNROLL for (int j = 0; j < NU; ++j) grad[NU * k + j] = su[j] + (2 * ru(j)) * uk[j];
+        PANTR_UNROLL for (int j = 0; j < NU; ++j) grad[NU * k + j] = COST ? su[j] + (2 * ru(j)) * uk[j] : su[j];
         if (k > 0) { // lambda_0 is not needed: c(x_0) and l_x(x_0) do not depend on u
             G::con_vjp(x, sc, w.yh + NC * k, ax);
-            PANTR_UNROLL for (int i = 0; i < NX; ++i) lam[i] = (s[i] + dcost_x(x, i, false)) + ax[i];
+            PANTR_UNROLL for (int i = 0; i < NX; ++i) lam[i] = COST ? (s[i] + dcost_x(x, i, false)) + ax[i] : s[i] + ax[i];
         }
     }
 }

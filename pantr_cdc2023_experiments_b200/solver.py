@@ -105,6 +105,106 @@ class BatchedProblem:
                                                      _ptr(yhat), _ptr(Hv)))
         return psi, grad, yhat, Hv
 
+    # ---- TypeErasedProblem API surface, batched (problem/type-erased-problem.hpp:228-571): every method
+    # takes the per-instance initial states x0 [B, nx] first (the NLP parameter), then the reference's
+    # arguments with a leading batch axis, and returns the reference's outputs. ----
+    def _xy(self, x0, x, y=None, Sigma=None, v=None):
+        B = np.shape(x)[0]
+        x0 = self.x0 if x0 is None else x0
+        out = [B, _f64(x0, (B, self.nx), "x0"), _f64(x, (B, self.n), "x")]
+        for a, shape, nm in ((y, (B, self.m), "y"), (Sigma, (B, self.m), "Sigma"), (v, (B, self.n), "v")):
+            out.append(None if (a is None or shape[1] == 0) else _f64(a, shape, nm))
+        return out
+
+    def eval_f(self, x, x0=None):
+        B, x0, x, *_ = self._xy(x0, x); f = np.empty(B)
+        _lib.check(_lib.load().pantr_b200_eval_f_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(f)))
+        return f
+
+    def eval_grad_f(self, x, x0=None):
+        B, x0, x, *_ = self._xy(x0, x); g = np.empty((B, self.n))
+        _lib.check(_lib.load().pantr_b200_eval_grad_f_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(g)))
+        return g
+
+    def eval_f_grad_f(self, x, x0=None):
+        B, x0, x, *_ = self._xy(x0, x); f = np.empty(B); g = np.empty((B, self.n))
+        _lib.check(_lib.load().pantr_b200_eval_f_grad_f_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(f), _ptr(g)))
+        return f, g
+
+    def eval_g(self, x, x0=None):
+        B, x0, x, *_ = self._xy(x0, x); g = np.empty((B, self.m))
+        _lib.check(_lib.load().pantr_b200_eval_g_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(g)))
+        return g
+
+    def eval_grad_g_prod(self, x, y, x0=None):
+        B, x0, x, y, *_ = self._xy(x0, x, y); out = np.empty((B, self.n))
+        _lib.check(_lib.load().pantr_b200_eval_grad_g_prod_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(y), _ptr(out)))
+        return out
+
+    def eval_grad_L(self, x, y, x0=None):
+        B, x0, x, y, *_ = self._xy(x0, x, y); out = np.empty((B, self.n))
+        _lib.check(_lib.load().pantr_b200_eval_grad_L_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(y), _ptr(out)))
+        return out
+
+    def eval_hess_L_prod(self, x, y, scale, v, x0=None):
+        B, x0, x, y, _, v = self._xy(x0, x, y, None, v); Hv = np.empty((B, self.n))
+        _lib.check(_lib.load().pantr_b200_eval_hess_L_prod_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(y),
+                                                                 float(scale), _ptr(v), _ptr(Hv)))
+        return Hv
+
+    def eval_hess_psi_prod(self, x, y, Sigma, scale, v, x0=None):
+        B, x0, x, y, Sigma, v = self._xy(x0, x, y, Sigma, v); Hv = np.empty((B, self.n))
+        _lib.check(_lib.load().pantr_b200_eval_hess_psi_prod_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(y),
+                                                                   _ptr(Sigma), float(scale), _ptr(v), _ptr(Hv)))
+        return Hv
+
+    def eval_psi(self, x, y, Sigma, x0=None):
+        B, x0, x, y, Sigma, _ = self._xy(x0, x, y, Sigma); psi = np.empty(B)
+        yhat = np.empty((B, self.m))
+        _lib.check(_lib.load().pantr_b200_eval_psi_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(y), _ptr(Sigma),
+                                                         _ptr(yhat) if self.m else None, _ptr(psi)))
+        return psi, yhat
+
+    def eval_grad_psi(self, x, y, Sigma, x0=None):
+        B, x0, x, y, Sigma, _ = self._xy(x0, x, y, Sigma); g = np.empty((B, self.n))
+        _lib.check(_lib.load().pantr_b200_eval_grad_psi_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(y),
+                                                              _ptr(Sigma), _ptr(g)))
+        return g
+
+    def eval_psi_grad_psi(self, x, y, Sigma, x0=None):
+        B, x0, x, y, Sigma, _ = self._xy(x0, x, y, Sigma); psi = np.empty(B); g = np.empty((B, self.n))
+        _lib.check(_lib.load().pantr_b200_eval_psi_grad_psi_batch(self._probe.h, B, _ptr(x0), _ptr(x), _ptr(y),
+                                                                  _ptr(Sigma), _ptr(psi), _ptr(g)))
+        return psi, g
+
+    def eval_prox_grad_step(self, gamma, x, grad_psi):
+        B = np.shape(x)[0]
+        x = _f64(x, (B, self.n), "x"); g = _f64(grad_psi, (B, self.n), "grad_psi")
+        xh, p = np.empty((B, self.n)), np.empty((B, self.n))
+        _lib.check(_lib.load().pantr_b200_eval_prox_grad_step_batch(self._probe.h, B, float(gamma), _ptr(x), _ptr(g),
+                                                                    _ptr(xh), _ptr(p)))
+        return np.zeros(B), xh, p  # h(x_hat) = 0: no l1 term
+
+    def eval_proj_diff_g(self, z):
+        B = np.shape(z)[0]
+        z = _f64(z, (B, self.m), "z"); e = np.empty((B, self.m))
+        _lib.check(_lib.load().pantr_b200_eval_proj_diff_g_batch(self._probe.h, B, _ptr(z), _ptr(e)))
+        return e
+
+    def eval_proj_multipliers(self, y, M):
+        B = np.shape(y)[0]
+        y = np.array(_f64(y, (B, self.m), "y"))
+        _lib.check(_lib.load().pantr_b200_eval_proj_multipliers_batch(self._probe.h, B, _ptr(y), float(M)))
+        return y
+
+    def eval_inactive_indices_res_lna(self, gamma, x, grad_psi):
+        B = np.shape(x)[0]
+        x = _f64(x, (B, self.n), "x"); g = _f64(grad_psi, (B, self.n), "grad_psi")
+        J = np.zeros((B, self.n), dtype=np.int32); nJ = np.zeros(B, dtype=np.int32)
+        _lib.check(_lib.load().pantr_b200_eval_inactive_indices_res_lna_batch(self._probe.h, B, float(gamma), _ptr(x),
+                                                                              _ptr(g), _ptr(J), _ptr(nJ)))
+        return [J[b, :nJ[b]].copy() for b in range(B)]
+
     # "simulate_dynamics" extra function (problems/problems/formulation.hpp:258-261)
     def simulate_dynamics(self, x, u):
         B = np.shape(x)[0]

@@ -12,3 +12,6 @@ echo "bench/ncu rc=$?"; cat gpurun_out/bench_$TAG.json; tail -3 gpurun_out/bench
 timeout 300 python tests/quick_bench.py 60 2368 > gpurun_out/quick_small_$TAG.log 2>&1 && \
 timeout 1500 ncu --set full --clock-control none --import-source on -k regex:solve_kernel -s 2 -c 1 -o gpurun_out/full_$TAG python tests/quick_bench.py 60 2368 > gpurun_out/ncu_full_$TAG.log 2>&1
 echo "ncu full rc=$?"; cat gpurun_out/quick_small_$TAG.log; ls -la gpurun_out/
+# one --set full capture of the bench's own timed launch shape (B = 16384 warm solve): DRAM traffic per launch
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:solve_kernel -s 4 -c 1 -o gpurun_out/fullbench_$TAG python bench.py --no-cpu-baseline --steps 1 --warmup 3 > gpurun_out/ncu_fullbench_$TAG.log 2>&1
+echo "ncu fullbench rc=$?"

@@ -93,3 +93,21 @@ def solve_batch(pid, N, par, x0, u, y=None, nthreads=1):
     assert load().oracle_solve_batch(pid, N, P(par), C.c_long(B), P(np.ascontiguousarray(x0)), P(u), P(y), P(st),
                                      nthreads) == 0
     return u, y, st
+
+
+FN = {"f": 0, "grad_f": 1, "f_grad_f": 2, "g": 3, "grad_g_prod": 4, "grad_L": 5, "hess_L_prod": 6,
+      "hess_psi_prod": 7, "prox_grad_step": 8, "proj_diff_g": 9, "proj_multipliers": 10, "inactive_indices": 11}
+
+
+def problem_eval(pid, N, fn, x0=None, x=None, y=None, Sigma=None, v=None, scalar=1.0):
+    """One member of the problem plugin table for one instance (oracle_problem_eval)."""
+    n, m, nx, nu = dims(pid, N)
+    c = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+    x0, x, y, Sigma, v = c(x0), c(x), c(y), c(Sigma), c(v)
+    s = C.c_double(0.0); cnt = C.c_int(0)
+    on, on2, om = np.zeros(n), np.zeros(n), np.zeros(max(m, 1))
+    oi = np.zeros(n, dtype=np.int32)
+    rc = load().oracle_problem_eval(pid, N, FN[fn], P(x0), P(x), P(y), P(Sigma), P(v), C.c_double(scalar),
+                                    C.byref(s), P(on), P(on2), P(om), P(oi), C.byref(cnt))
+    assert rc == 0
+    return {"s": s.value, "n": on, "n2": on2, "m": om[:m], "J": oi[:cnt.value].copy()}
