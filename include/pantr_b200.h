@@ -213,6 +213,11 @@ int pantr_b200_simulate_dynamics_batch_device(pantr_b200_solver *s, int64_t B, c
 int pantr_b200_shift_warm_start_device(pantr_b200_solver *s, int64_t B, double *d_u, double *d_y,
                                        void *stream);
 
+/* How instances map onto the GPU for the next solves: 0 = automatic (default), 1 = one warp per instance,
+ * 2 = one thread per instance (32 per warp; quadcopter models only, ignored for the hanging chain).
+ * Automatic picks 2 for the quadcopters when B >= 256.  Results are bit-identical in both mappings. */
+int pantr_b200_set_exec_mode(pantr_b200_solver *s, int mode);
+
 /* Optional per-iteration trace of one instance of the next solve_batch call (debug / parity):
  * rows of 11 doubles {k, psi, fbe, gamma, eps, radius, rho, q_model, nJ, cg_iters, accepted}. */
 int pantr_b200_set_trace(pantr_b200_solver *s, int64_t instance, int max_rows);

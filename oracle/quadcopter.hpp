@@ -52,11 +52,11 @@ struct Quadcopter : Problem {
     real_t eval_psi_impl(const real_t *x, const real_t *y, const real_t *S, real_t *yhat) const override {
         hvp_ready = false;
         real_t f = pantr::quad::rollout<G>(N, x0.data(), x, w);
-        return f + pantr::quad::al_terms<G>(N, w, y, S, yhat, nullptr);
+        return f + pantr::quad::al_terms<G>(N, w, y, S, yhat, yhat != nullptr, static_cast<real_t *>(nullptr), false);
     }
     real_t eval_psi_grad_psi_impl(const real_t *x, const real_t *y, const real_t *S, real_t *grad) const override {
         real_t f   = pantr::quad::rollout<G>(N, x0.data(), x, w);
-        real_t psi = f + pantr::quad::al_terms<G>(N, w, y, S, w.yh, w.wact);
+        real_t psi = f + pantr::quad::al_terms<G>(N, w, y, S, w.yh, true, w.wact, true);
         pantr::quad::adjoint<G>(N, x, w, grad);
         hvp_ready = true;
         return psi;

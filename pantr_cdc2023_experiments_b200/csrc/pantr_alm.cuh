@@ -10,7 +10,7 @@
     // BoxConstrProblem::eval_proj_multipliers (box-constr-problem.hpp:119-143), penalty_alm_split = 0
     __device__ void proj_multipliers(double M) {
         ++st.ev_proj_multipliers;
-        for (int i = lane_id(); i < m; i += 32) {
+        for (int i = E::first(); i < m; i += E::STEP) {
             double y_lb = Model::D_lb(i, mdl.N) == -INFINITY ? 0.0 : -M;
             double y_ub = Model::D_ub(i, mdl.N) == +INFINITY ? 0.0 : +M;
             double v = y[i];
@@ -18,30 +18,30 @@
             v = y_ub < v ? y_ub : v; // std::min(., y_ub)
             y[i] = v;
         }
-        __syncwarp();
+        E::sync();
     }
 
     // alm-helpers.tpp:16-45 (monotone = true)
-    __device__ void update_penalty_weights(double Delta, bool first_iter, const double *e, const double *old_e,
-                                           double norm_e, double old_norm_e, const double *S_old, double *S) {
+    __device__ void update_penalty_weights(double Delta, bool first_iter, CVec e, CVec old_e, double norm_e,
+                                           double old_norm_e, CVec S_old, Vec S) {
         const auto &a = P.alm;
         const double theta = a.rel_penalty_increase_threshold;
-        if (norm_e <= a.dual_tolerance) { vcopy(S, S_old, m); __syncwarp(); return; }
+        if (norm_e <= a.dual_tolerance) { xcopy<E>(S, S_old, m); E::sync(); return; }
         if (a.single_penalty_factor) {
             if (first_iter || norm_e > theta * old_norm_e) {
                 double new_S = fmin(a.max_penalty, Delta * S_old[0]);
-                __syncwarp();
-                for (int i = lane_id(); i < m; i += 32) S[i] = new_S;
-            } else vcopy(S, S_old, m);
+                E::sync();
+                for (int i = E::first(); i < m; i += E::STEP) S[i] = new_S;
+            } else xcopy<E>(S, S_old, m);
         } else {
-            for (int i = lane_id(); i < m; i += 32) {
+            for (int i = E::first(); i < m; i += E::STEP) {
                 if (first_iter || fabs(e[i]) > theta * fabs(old_e[i]))
                     S[i] = fmin(a.max_penalty, fmax(Delta * fabs(e[i]) / norm_e, 1.0) * S_old[i]);
                 else
                     S[i] = S_old[i];
             }
         }
-        __syncwarp();
+        E::sync();
     }
 
     // alm.tpp:19-226.  x, y are this->x / this->y (in/out).
@@ -49,26 +49,26 @@
         const auto &a = P.alm;
         st.status = PANTR_B200_BUSY;
         if (Model::NC == 0) { // alm.tpp:29-52 (m == 0  <=>  the model has no general constraints)
-            InnerResult ps = inner_solve(a.tolerance, true, nullptr);
+            InnerResult ps = inner_solve(a.tolerance, true, Vec{}, false);
             accumulate(ps);
             st.eps = ps.eps; st.delta = 0; st.norm_penalty = 0; st.outer_iterations = 1;
             st.status = ps.status;
             return;
         }
-        double *error_1 = e1, *error_2 = e2, *S = Sig, *S_old = Sig_old;
+        Vec error_1 = e1, error_2 = e2, S = Sig, S_old = Sig_old;
         double norm_e_1 = nan(""), norm_e_2 = nan("");
         if (a.initial_penalty > 0) {
-            for (int i = lane_id(); i < m; i += 32) S[i] = a.initial_penalty;
+            for (int i = E::first(); i < m; i += E::STEP) S[i] = a.initial_penalty;
         } else { // alm-helpers.tpp:47-59
             ++st.ev_f; ++st.ev_g;
             double f0 = mdl.eval_f(x);
             mdl.eval_g(x, e1);
-            double g0sq = vsqnorm(e1, m);
+            double g0sq = xsqnorm<E>(e1, m);
             double sigma = a.initial_penalty_factor * fmax(1.0, fabs(f0)) / fmax(1.0, 0.5 * g0sq);
             sigma = sigma < a.min_penalty ? a.min_penalty : (a.max_penalty < sigma ? a.max_penalty : sigma);
-            for (int i = lane_id(); i < m; i += 32) S[i] = sigma;
+            for (int i = E::first(); i < m; i += E::STEP) S[i] = sigma;
         }
-        __syncwarp();
+        E::sync();
         double eps_ = a.initial_tolerance, eps_old = nan("");
         double Delta = a.penalty_update_factor, rho = a.tolerance_update_factor;
         unsigned num_successful_iters = 0, initial_penalty_reduced = 0, penalty_reduced = 0;
@@ -81,7 +81,7 @@
             bool out_of_iter       = i + 1 == a.max_iter;
             bool overwrite_results = out_of_iter || out_of_penalty_factor_updates;
             Sig = S; // the inner solver and the model read this->Sig
-            InnerResult ps = inner_solve(eps_, overwrite_results, error_2);
+            InnerResult ps = inner_solve(eps_, overwrite_results, error_2, true);
             bool inner_converged = ps.status == PANTR_B200_CONVERGED;
             accumulate(ps);
             bool backtrack = !inner_converged && !overwrite_results;
@@ -93,23 +93,23 @@
                     eps_ = fmax(rho * eps_old, a.tolerance);
                     ++penalty_reduced;
                 } else {
-                    for (int j = lane_id(); j < m; j += 32) S[j] *= a.initial_penalty_lower;
-                    __syncwarp();
+                    for (int j = E::first(); j < m; j += E::STEP) S[j] *= a.initial_penalty_lower;
+                    E::sync();
                     eps_ *= a.initial_tolerance_increase;
                     ++initial_penalty_reduced;
                 }
             } else { // alm.tpp:190-222
-                { double *t = error_2; error_2 = error_1; error_1 = t; }
+                { Vec t = error_2; error_2 = error_1; error_1 = t; }
                 norm_e_2 = norm_e_1;
-                norm_e_1 = vnorm_inf(error_1, m);
+                norm_e_1 = xnorm_inf<E>(error_1, m);
                 bool alm_converged = ps.eps <= a.tolerance && inner_converged && norm_e_1 <= a.dual_tolerance;
                 if (alm_converged || out_of_iter) {
-                    st.eps = ps.eps; st.delta = norm_e_1; st.norm_penalty = vnorm2(S, m);
+                    st.eps = ps.eps; st.delta = norm_e_1; st.norm_penalty = xnorm2<E>(S, m);
                     st.outer_iterations = i + 1;
                     st.status = alm_converged ? PANTR_B200_CONVERGED : PANTR_B200_MAX_ITER;
                     return;
                 }
-                { double *t = S_old; S_old = S; S = t; }
+                { Vec t = S_old; S_old = S; S = t; }
                 update_penalty_weights(Delta, num_successful_iters == 0, error_1, error_2, norm_e_1, norm_e_2, S_old, S);
                 eps_old = eps_;
                 eps_    = fmax(rho * eps_, a.tolerance);

@@ -67,6 +67,40 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
     }
 }
 
+// ---- thread-per-instance variant (ThreadExec, exec_policy.cuh): 32 instances per warp, vectors
+// interleaved across the warp.  For the small-state models whose sweeps are sequential chains. ----
+template <class Model>
+__global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel_thread(const __grid_constant__ SolverParams P,
+                                                                             const __grid_constant__ KernelArgs A) {
+    IterScalars it[3];
+    const int lane = lane_id();
+    SVecT<double> ws{A.ws + size_t(blockIdx.x) * A.ws_stride + lane};
+    for (;;) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(A.counter, 32ULL);
+        base = __shfl_sync(FULL, base, 0);
+        if (base >= (unsigned long long)A.B) break;
+        const long long b = (long long)base + lane;
+        if (b < A.B) {
+            long long t0 = clock64();
+            Model mdl;
+            mdl.init(A.N, A.x0 + b * A.nx, ws);
+            Pantr<Model, ThreadExec> S(mdl, P, it, A.n, A.m, ws + Model::traj_doubles(A.N));
+            memset(&S.st, 0, sizeof(S.st));
+            for (int i = 0; i < A.n; ++i) S.x[i] = A.u[b * A.n + i];
+            for (int i = 0; i < A.m; ++i) S.y[i] = A.y[b * A.m + i];
+            S.tracing = A.trace.rows != nullptr && b == A.trace.instance;
+            S.tr = A.trace;
+            S.alm_solve();
+            for (int i = 0; i < A.n; ++i) A.u[b * A.n + i] = S.x[i];
+            for (int i = 0; i < A.m; ++i) A.y[b * A.m + i] = S.y[i];
+            S.st.cycles = (unsigned long long)(clock64() - t0);
+            A.stats[b] = S.st;
+        }
+        __syncwarp();
+    }
+}
+
 // ---- batched problem-function evaluation (eval_psi_grad_psi / eval_psi / eval_hess_psi_prod) ----
 struct EvalArgs {
     int N, n, m, nx;

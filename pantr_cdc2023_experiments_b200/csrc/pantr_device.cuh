@@ -8,7 +8,7 @@
 // All scalars are warp-uniform; vectors are lane-strided in the instance workspace.
 #pragma once
 #include "../../include/pantr_b200.h"
-#include "warp_utils.cuh"
+#include "exec_policy.cuh"
 
 namespace pantr {
 
@@ -24,19 +24,22 @@ struct IterScalars { double psi_x, psi_xh, gamma, L, pTp, gTp, h; };
 struct Trace { double *rows; int *n_rows; int max_rows; long long instance; };
 
 // Number of n-vectors / m-vectors / ints in the workspace (see Workspace::bind)
-constexpr int WS_NVEC = 25, WS_MVEC = 10;
+constexpr int WS_NVEC = 26, WS_MVEC = 10;
 
-template <class Model>
+template <class Model, class E = WarpExec>
 struct Pantr {
+    using Vec = typename E::Vec;
+    using CVec = typename E::CVec;
+    using IVec = typename E::IVec;
     Model &mdl;
     const SolverParams &P;
     IterScalars *it; // [3] in shared memory
     int n, m;
     // iterate storage (slot-major)
-    double *X, *XH, *G, *PP, *YH;
-    double *q, *work, *work2, *rJ, *qJ, *z, *r, *d, *Bd, *we, *wn1, *wn2, *gxh;
-    double *x, *y, *Sig, *Sig_old, *e1, *e2; // ALM-level vectors
-    int *JK;
+    Vec X, XH, G, PP, YH;
+    Vec q, work, work2, rJ, qJ, z, r, d, Bd, we, wn1, wn2, gxh;
+    Vec x, y, Sig, Sig_old, e1, e2; // ALM-level vectors
+    IVec JK;
     pantr_b200_stats st;
     unsigned cg_last;
     bool tracing;
@@ -47,20 +50,26 @@ struct Pantr {
     __host__ __device__ static size_t smem_bytes(int n, int set) {
         return set == 0 ? 0 : (set == 1 ? size_t(4) * n * 8 : size_t(6) * n * 8 + size_t(n + 2) / 2 * 8);
     }
-    __device__ Pantr(Model &mdl_, const SolverParams &P_, IterScalars *it_, int n_, int m_, double *ws,
+    __device__ Pantr(Model &mdl_, const SolverParams &P_, IterScalars *it_, int n_, int m_, Vec ws,
                      double *sm = nullptr, int smem_set = 0)
         : mdl(mdl_), P(P_), it(it_), n(n_), m(m_) {
-        double *p = ws;
+        Vec p = ws;
         X = p; p += 3 * n; XH = p; p += 3 * n; G = p; p += 3 * n; PP = p; p += 3 * n;
         q = p; p += n; work = p; p += n; work2 = p; p += n; rJ = p; p += n; qJ = p; p += n;
         z = p; p += n; r = p; p += n; d = p; p += n; Bd = p; p += n; we = p; p += n;
         wn1 = p; p += n; wn2 = p; p += n; gxh = p; p += n; // 12 + 13 = 25 n-vectors
-        YH = p; p += 3 * m; x = nullptr;
+        YH = p; p += 3 * m;
+        x = p; p += n; // ThreadExec only: the iterate, copied in / out of the batch arrays (26th n-vector)
         y = p; p += m; Sig = p; p += m; Sig_old = p; p += m; e1 = p; p += m; e2 = p; p += m;
         p += 2 * m; // spare (10 m-vectors)
-        JK = reinterpret_cast<int *>(p);
-        if (smem_set >= 1) { z = sm; r = sm + n; d = sm + 2 * n; Bd = sm + 3 * n; }
-        if (smem_set >= 2) { work = sm + 4 * n; work2 = sm + 5 * n; JK = reinterpret_cast<int *>(sm + 6 * n); }
+        if constexpr (E::THREAD) {
+            // 32 n ints of the warp's block fit in its 32 (n / 2 + 2) doubles; the lane offset is in int units
+            JK = IVec{reinterpret_cast<int *>(p.p - lane_id()) + lane_id()};
+        } else {
+            JK = reinterpret_cast<int *>(p);
+            if (smem_set >= 1) { z = sm; r = sm + n; d = sm + 2 * n; Bd = sm + 3 * n; }
+            if (smem_set >= 2) { work = sm + 4 * n; work2 = sm + 5 * n; JK = reinterpret_cast<int *>(sm + 6 * n); }
+        }
     }
     __host__ __device__ static size_t ws_doubles(int n, int m) {
         return size_t(WS_NVEC) * n + size_t(WS_MVEC) * m + (n + 1) / 2 + 2;
@@ -73,10 +82,9 @@ struct Pantr {
         it[s].psi_x = v;
     }
     // box-constr-problem.hpp:59-64 ; returns h = 0
-    __device__ __noinline__ void prox_grad_step_raw(double gamma, const double *xx, const double *g, double *xh,
-                                       double *p) {
+    __device__ __noinline__ void prox_grad_step_raw(double gamma, CVec xx, CVec g, Vec xh, Vec p) {
         ++st.ev_prox_grad_step;
-        for (int i = lane_id(); i < n; i += 32) {
+        for (int i = E::first(); i < n; i += E::STEP) {
             double xi = xx[i], s = -gamma * g[i];
             double lo = Model::C_lb(i) - xi, hi = Model::C_ub(i) - xi;
             double t  = s < lo ? lo : s;
@@ -87,8 +95,8 @@ struct Pantr {
     }
     __device__ __noinline__ void eval_prox_grad_step(int s) { // pantr.tpp:88-92
         prox_grad_step_raw(it[s].gamma, X + s * n, G + s * n, XH + s * n, PP + s * n);
-        __syncwarp();
-        double pTp = vsqnorm(PP + s * n, n), gTp = vdot(PP + s * n, G + s * n, n);
+        E::sync();
+        double pTp = xsqnorm<E>(PP + s * n, n), gTp = xdot<E>(PP + s * n, G + s * n, n);
         it[s].h = 0; it[s].pTp = pTp; it[s].gTp = gTp;
     }
     __device__ __noinline__ void eval_psi_xh(int s) { // pantr.tpp:93-95
@@ -105,14 +113,14 @@ struct Pantr {
     }
     __device__ __noinline__ void backtrack_qub(int s) { // pantr.tpp:107-115
         while (it[s].L < P.pantr.L_max && qub_violated(s)) {
-            __syncwarp();
+            E::sync();
             double g2 = it[s].gamma / 2, L2 = it[s].L * 2;
-            __syncwarp();
+            E::sync();
             it[s].gamma = g2; it[s].L = L2;
-            __syncwarp();
+            E::sync();
             eval_prox_grad_step(s);
             eval_psi_xh(s);
-            __syncwarp();
+            E::sync();
         }
     }
 #include "pantr_direction.cuh"

@@ -4,60 +4,39 @@
     // eval_inactive_indices_res_lna (box-constr-problem.hpp:151-185) + IndexSet::compute_complement
     // (util/index-set.hpp:46-50): ascending J in JK[0..nJ), ascending K in JK[nJ..n), by
     // ballot / prefix-popcount compaction.
-    __device__ __noinline__ int inactive_indices(double gamma, const double *xx, const double *g) {
+    __device__ __noinline__ int inactive_indices(double gamma, CVec xx, CVec g) {
         ++st.ev_inactive_indices_res_lna;
-        const int lane = lane_id();
-        const unsigned lt = (1u << lane) - 1u;
-        int nJ = 0;
-        for (int i0 = 0; i0 < n; i0 += 32) {
-            int i = i0 + lane;
-            bool in = false;
-            if (i < n) {
-                double x_fw = xx[i] - gamma * g[i];
-                in = Model::C_lb(i) < x_fw && x_fw < Model::C_ub(i);
-            }
-            unsigned b = __ballot_sync(FULL, in);
-            if (in) JK[nJ + __popc(b & lt)] = i;
-            nJ += __popc(b);
-        }
-        int nK = 0;
-        for (int i0 = 0; i0 < n; i0 += 32) {
-            int i = i0 + lane;
-            bool out = false;
-            if (i < n) {
-                double x_fw = xx[i] - gamma * g[i];
-                out = !(Model::C_lb(i) < x_fw && x_fw < Model::C_ub(i));
-            }
-            unsigned b = __ballot_sync(FULL, out);
-            if (out) JK[nJ + nK + __popc(b & lt)] = i;
-            nK += __popc(b);
-        }
-        __syncwarp();
+        auto inside = [&](int i) {
+            double x_fw = xx[i] - gamma * g[i];
+            return Model::C_lb(i) < x_fw && x_fw < Model::C_ub(i);
+        };
+        int nJ = E::compact(n, JK, 0, inside);
+        (void)E::compact(n, JK, nJ, [&](int i) { return !inside(i); });
+        E::sync();
         return nJ;
     }
 
     // hess_vec_mult of newton-tr.hpp:134-149: Bp = (H work)(J), work(J) = p, zero elsewhere
-    __device__ __noinline__ void hess_vec_mult(const double *xx, const double *p, double *Bp, int nJ) {
-        const int *J = JK;
-        for (int i = lane_id(); i < n; i += 32) work[i] = 0.0;
-        __syncwarp();
-        for (int j = lane_id(); j < nJ; j += 32) work[J[j]] = p[j];
+    __device__ __noinline__ void hess_vec_mult(CVec xx, CVec p, Vec Bp, int nJ) {
+        const IVec J = JK;
+        for (int i = E::first(); i < n; i += E::STEP) work[i] = 0.0;
+        E::sync();
+        for (int j = E::first(); j < nJ; j += E::STEP) work[J[j]] = p[j];
         ++st.ev_hess_psi_prod;
         mdl.hess_psi_prod(xx, y, Sig, work, work2);
-        for (int j = lane_id(); j < nJ; j += 32) Bp[j] = work2[J[j]];
-        __syncwarp();
+        for (int j = E::first(); j < nJ; j += E::STEP) Bp[j] = work2[J[j]];
+        E::sync();
     }
     // eval lambda of steihaugcg.hpp:62-65
-    __device__ __noinline__ double cg_eval(const double *xx, const double *p, const double *g, int nJ) {
+    __device__ __noinline__ double cg_eval(CVec xx, CVec p, CVec g, int nJ) {
         hess_vec_mult(xx, p, we, nJ);
-        return vdot(p, g, nJ) + 0.5 * vdot(p, we, nJ);
+        return xdot<E>(p, g, nJ) + 0.5 * xdot<E>(p, we, nJ);
     }
     // steihaugcg.hpp:122-140
-    __device__ __noinline__ void boundaries(const double *zz, const double *dd_, int nJ, double radius, double &lo,
-                               double &hi) {
-        double a = vsqnorm(dd_, nJ);
-        double b = 2 * vdot(zz, dd_, nJ);
-        double c = vsqnorm(zz, nJ) - radius * radius;
+    __device__ __noinline__ void boundaries(CVec zz, CVec dd_, int nJ, double radius, double &lo, double &hi) {
+        double a = xsqnorm<E>(dd_, nJ);
+        double b = 2 * xdot<E>(zz, dd_, nJ);
+        double c = xsqnorm<E>(zz, nJ) - radius * radius;
         double sqrt_discriminant = sqrt(b * b - 4 * a * c);
         double aux = b + copysign(sqrt_discriminant, b);
         double ta  = -aux / (2 * a);
@@ -65,11 +44,10 @@
         lo = fmin(ta, tb); hi = fmax(ta, tb);
     }
     // steihaugcg.hpp:39-117 ; g = rJ, step -> s (both compressed, length nJ)
-    __device__ __noinline__ double steihaug(const double *xx, const double *g, int nJ, double radius, double *s) {
-        const int lane = lane_id();
-        for (int j = lane; j < nJ; j += 32) { double gj = g[j]; z[j] = 0.0; r[j] = gj; d[j] = -gj; }
-        __syncwarp();
-        double r_sq = vsqnorm(r, nJ), grad_mag = vnorm2(g, nJ);
+    __device__ __noinline__ double steihaug(CVec xx, CVec g, int nJ, double radius, Vec s) {
+        for (int j = E::first(); j < nJ; j += E::STEP) { double gj = g[j]; z[j] = 0.0; r[j] = gj; d[j] = -gj; }
+        E::sync();
+        double r_sq = xsqnorm<E>(r, nJ), grad_mag = xnorm2<E>(g, nJ);
         double tolerance = fmin(P.cg.tol_max,
                                 P.cg.tol_scale * grad_mag * fmin(P.cg.tol_scale_root, sqrt(grad_mag)));
         long long i = 0;
@@ -78,66 +56,63 @@
         while (true) {
             ++cg_last;
             hess_vec_mult(xx, d, Bd, nJ);
-            double dBd = vdot(d, Bd, nJ);
+            double dBd = xdot<E>(d, Bd, nJ);
             if (dBd <= 0) {
                 double ta, tb;
                 boundaries(z, d, nJ, radius, ta, tb);
-                double *pa = r, *pb = d; // storage reuse as in the reference
-                for (int j = lane; j < nJ; j += 32) {
+                Vec pa = r, pb = d; // storage reuse as in the reference
+                for (int j = E::first(); j < nJ; j += E::STEP) {
                     double zj = z[j], dj = d[j];
                     pa[j] = zj + ta * dj;
                     pb[j] = zj + tb * dj;
                 }
-                __syncwarp();
+                E::sync();
                 double q_a = cg_eval(xx, pa, g, nJ), q_b = cg_eval(xx, pb, g, nJ);
                 double q_min = fmin(q_a, q_b);
-                if (q_a == q_min) { vcopy(s, pa, nJ); __syncwarp(); return q_a; }
-                else              { vcopy(s, pb, nJ); __syncwarp(); return q_b; }
+                if (q_a == q_min) { xcopy<E>(s, pa, nJ); E::sync(); return q_a; }
+                else              { xcopy<E>(s, pb, nJ); E::sync(); return q_b; }
             }
             double alpha = r_sq / dBd;
-            for (int j = lane; j < nJ; j += 32) s[j] = z[j] + alpha * d[j];
-            __syncwarp();
-            if (vnorm2(s, nJ) >= radius) {
+            for (int j = E::first(); j < nJ; j += E::STEP) s[j] = z[j] + alpha * d[j];
+            E::sync();
+            if (xnorm2<E>(s, nJ) >= radius) {
                 double ta, tb;
                 boundaries(z, d, nJ, radius, ta, tb);
-                for (int j = lane; j < nJ; j += 32) s[j] = z[j] + tb * d[j];
-                __syncwarp();
+                for (int j = E::first(); j < nJ; j += E::STEP) s[j] = z[j] + tb * d[j];
+                E::sync();
                 return cg_eval(xx, s, g, nJ);
             }
-            for (int j = lane; j < nJ; j += 32) r[j] = r[j] + alpha * Bd[j];
-            __syncwarp();
-            double r_next_sq = vsqnorm(r, nJ);
+            for (int j = E::first(); j < nJ; j += E::STEP) r[j] = r[j] + alpha * Bd[j];
+            E::sync();
+            double r_next_sq = xsqnorm<E>(r, nJ);
             if (sqrt(r_next_sq) < tolerance || i > max_iter) return cg_eval(xx, s, g, nJ);
             double beta_next = r_next_sq / r_sq;
             r_sq             = r_next_sq;
-            for (int j = lane; j < nJ; j += 32) { d[j] = beta_next * d[j] - r[j]; z[j] = s[j]; }
-            __syncwarp();
+            for (int j = E::first(); j < nJ; j += E::STEP) { d[j] = beta_next * d[j] - r[j]; z[j] = s[j]; }
+            E::sync();
             ++i;
         }
     }
 
     // newton-tr.hpp:91-155 (exact Hessian branch). xx, pk, g: prox iterate. Returns q_model.
-    __device__ __noinline__ double direction_apply(double gamma, const double *xx, const double *pk, const double *g,
-                                      double radius, double *qk, int &nJ_out) {
-        const int lane = lane_id();
+    __device__ __noinline__ double direction_apply(double gamma, CVec xx, CVec pk, CVec g, double radius, Vec qk, int &nJ_out) {
         const int nJ = inactive_indices(gamma, xx, g), nK = n - nJ;
         nJ_out = nJ;
-        const int *J = JK, *K = JK + nJ;
+        const IVec J = JK, K = JK + nJ;
         const double mig = -1.0 / gamma;
-        for (int j = lane; j < nJ; j += 32) { int i = J[j]; rJ[j] = mig * pk[i]; qk[i] = 0.0; }
-        double part = 0;
-        for (int k = lane; k < nK; k += 32) { int i = K[k]; double pi = pk[i]; qk[i] = pi; part = part + pi * pi; }
-        double norm_qK_sq = warp_sum(part);
-        __syncwarp();
+        for (int j = E::first(); j < nJ; j += E::STEP) { int i = J[j]; rJ[j] = mig * pk[i]; qk[i] = 0.0; }
+        for (int k = E::first(); k < nK; k += E::STEP) { int i = K[k]; qk[i] = pk[i]; }
+        double norm_qK_sq = E::sum(nK, [&](int k) { double pi = pk[K[k]]; return pi * pi; });
+        E::sync();
         const double hvf = P.dir.hessian_vec_factor;
         if (hvf != 0) {
             ++st.ev_hess_psi_prod;
             mdl.hess_psi_prod(xx, y, Sig, qk, work);
-            for (int j = lane; j < nJ; j += 32) rJ[j] = rJ[j] + work[J[j]] * hvf;
-            __syncwarp();
+            for (int j = E::first(); j < nJ; j += E::STEP) rJ[j] = rJ[j] + work[J[j]] * hvf;
+            E::sync();
         }
         double qJ_model = steihaug(xx, rJ, nJ, radius, qJ);
-        for (int j = lane; j < nJ; j += 32) qk[J[j]] = qJ[j];
-        __syncwarp();
+        for (int j = E::first(); j < nJ; j += E::STEP) qk[J[j]] = qJ[j];
+        E::sync();
         return qJ_model - norm_qK_sq / (2 * gamma);
     }

@@ -6,49 +6,49 @@
     // panoc-helpers.tpp:62-137 (criteria that do not need grad psi(x_hat))
     __device__ __noinline__ double calc_error_stop_crit(int c) {
         const int crit = P.pantr.stop_crit;
-        const double *pk = PP + c * n;
+        const CVec pk = PP + c * n;
         switch (crit) {
-            case PANTR_B200_PROJ_GRAD_NORM: return vnorm_inf(pk, n);
-            case PANTR_B200_PROJ_GRAD_NORM2: return vnorm2(pk, n);
+            case PANTR_B200_PROJ_GRAD_NORM: return xnorm_inf<E>(pk, n);
+            case PANTR_B200_PROJ_GRAD_NORM2: return xnorm2<E>(pk, n);
             case PANTR_B200_PROJ_GRAD_UNIT_NORM:
                 prox_grad_step_raw(1.0, X + c * n, G + c * n, wn1, wn2);
-                __syncwarp();
-                return vnorm_inf(wn2, n);
+                E::sync();
+                return xnorm_inf<E>(wn2, n);
             case PANTR_B200_PROJ_GRAD_UNIT_NORM2:
                 prox_grad_step_raw(1.0, X + c * n, G + c * n, wn1, wn2);
-                __syncwarp();
-                return vnorm2(wn2, n);
-            case PANTR_B200_FPR_NORM: return vnorm_inf(pk, n) / it[c].gamma;
-            case PANTR_B200_FPR_NORM2: return vnorm2(pk, n) / it[c].gamma;
+                E::sync();
+                return xnorm2<E>(wn2, n);
+            case PANTR_B200_FPR_NORM: return xnorm_inf<E>(pk, n) / it[c].gamma;
+            case PANTR_B200_FPR_NORM2: return xnorm2<E>(pk, n) / it[c].gamma;
             default: return nan("");
         }
     }
 
     // x (in/out) lives in this->x ; y in this->y ; Sigma in this->Sig ; err_z -> errz (may be null)
-    __device__ __noinline__ InnerResult inner_solve(double tolerance_opt, bool always_overwrite, double *errz) {
+    __device__ __noinline__ InnerResult inner_solve(double tolerance_opt, bool always_overwrite, Vec errz, bool has_errz) {
         const auto &pp = P.pantr;
         int curr = 0, prox = 1, cand = 2;
         InnerResult res{PANTR_B200_BUSY, INFINITY, 0};
-        vcopy(X + curr * n, x, n); // pantr.tpp:195
-        __syncwarp();
+        xcopy<E>(X + curr * n, x, n); // pantr.tpp:195
+        E::sync();
         // ---- initial Lipschitz estimate: pantr.tpp:200-217, panoc-helpers.tpp:288-334 ----
         if (pp.Lipschitz.L_0 <= 0) {
             eval_psi_grad_psi(curr);
-            double *wx = XH + curr * n, *wg = G + cand * n, *hv = wn1;
-            for (int i = lane_id(); i < n; i += 32) {
+            Vec wx = XH + curr * n, wg = G + cand * n, hv = wn1;
+            for (int i = E::first(); i < n; i += E::STEP) {
                 double g = G[curr * n + i];
                 double hi = g > 0 ? fmax(g * pp.Lipschitz.epsilon, pp.Lipschitz.delta)
                                   : fmin(g * pp.Lipschitz.epsilon, -pp.Lipschitz.delta);
                 hv[i] = hi;
                 wx[i] = X[curr * n + i] - hi;
             }
-            __syncwarp();
-            double norm_h = vnorm2(hv, n);
+            E::sync();
+            double norm_h = xnorm2<E>(hv, n);
             ++st.ev_grad_psi;
             (void)mdl.eval_psi_grad_psi(wx, y, Sig, wg);
-            for (int i = lane_id(); i < n; i += 32) hv[i] = wg[i] - G[curr * n + i];
-            __syncwarp();
-            double L = vnorm2(hv, n) / norm_h;
+            for (int i = E::first(); i < n; i += E::STEP) hv[i] = wg[i] - G[curr * n + i];
+            E::sync();
+            double L = xnorm2<E>(hv, n) / norm_h;
             // std::clamp(L, L_min, L_max)
             L = L < pp.L_min ? pp.L_min : (pp.L_max < L ? pp.L_max : L);
             it[curr].L = L;
@@ -56,23 +56,23 @@
             it[curr].L = pp.Lipschitz.L_0;
             eval_psi_grad_psi(curr);
         }
-        __syncwarp();
+        E::sync();
         if (!isfinite(it[curr].L)) { res.status = PANTR_B200_NOT_FINITE; return res; }
         it[curr].gamma = pp.Lipschitz.Lgamma_factor / it[curr].L;
-        __syncwarp();
+        E::sync();
         eval_prox_grad_step(curr); // pantr.tpp:221-223
         eval_psi_xh(curr);
         backtrack_qub(curr);
 
         unsigned k = 0, no_progress = 0;
         double Delta = pp.initial_radius; // pantr.tpp:232-235
-        if (!isfinite(Delta) || Delta == 0) Delta = 0.1 * vnorm2(G + curr * n, n);
+        if (!isfinite(Delta) || Delta == 0) Delta = 0.1 * xnorm2<E>(G + curr * n, n);
         Delta      = fmax(Delta, pp.min_radius);
         double rho = nan("");
         const double tolerance = tolerance_opt > 0 ? tolerance_opt : 1e-8;
 
         while (true) {
-            __syncwarp();
+            E::sync();
             double eps_k = calc_error_stop_crit(curr);
             // check_all_stop_conditions: panoc-helpers.tpp:215-249 (no wall clock / stop signal on device)
             int stop = eps_k <= tolerance                    ? PANTR_B200_CONVERGED
@@ -82,32 +82,32 @@
                                                              : PANTR_B200_BUSY;
             if (stop != PANTR_B200_BUSY) { // pantr.tpp:269-298
                 if (stop == PANTR_B200_CONVERGED || always_overwrite) {
-                    const double *yh = YH + curr * m;
-                    for (int i = lane_id(); i < m; i += 32) {
+                    const CVec yh = YH + curr * m;
+                    for (int i = E::first(); i < m; i += E::STEP) {
                         double yhi = yh[i];
-                        if (errz) errz[i] = (1.0 / Sig[i]) * (yhi - y[i]);
+                        if (has_errz) errz[i] = (1.0 / Sig[i]) * (yhi - y[i]);
                         y[i] = yhi;
                     }
-                    vcopy(x, XH + curr * n, n);
+                    xcopy<E>(x, XH + curr * n, n);
                 }
                 st.final_gamma = it[curr].gamma; st.final_psi = it[curr].psi_xh;
                 st.final_h = it[curr].h; st.final_fbe = fbe(curr);
                 res.status = stop; res.eps = eps_k; res.iterations = k;
-                __syncwarp();
+                E::sync();
                 return res;
             }
             // ---- compute_FBS_step: pantr.tpp:303-319 ----
             // The reference evaluates grad_L(x_hat, y_hat) here and immediately overwrites the
             // result with psi_grad_psi(prox.x): numerically dead, so only counted.
             ++st.ev_grad_L;
-            vcopy(X + prox * n, XH + curr * n, n);
+            xcopy<E>(X + prox * n, XH + curr * n, n);
             double cg_ = it[curr].gamma, cL_ = it[curr].L, cpsi = it[curr].psi_xh;
-            __syncwarp();
+            E::sync();
             it[prox].gamma = cg_; it[prox].L = cL_; it[prox].psi_x = cpsi;
-            __syncwarp();
+            E::sync();
             eval_psi_grad_psi(prox);
             eval_prox_grad_step(prox);
-            __syncwarp();
+            E::sync();
 
             bool accept_candidate = false;
             const bool accelerated_iteration = true; // k > 0 || has_initial_direction() (newton-tr.hpp:79)
@@ -117,20 +117,20 @@
                 // compute_trust_region_step: pantr.tpp:371-392
                 q_model = direction_apply(it[prox].gamma, X + prox * n, PP + prox * n, G + prox * n, Delta, q, nJ);
                 cgi = cg_last; st.cg_iterations += cg_last;
-                if (!vall_finite(q, n)) { ++st.direction_failures; q_model = INFINITY; }
+                if (!xall_finite<E>(q, n)) { ++st.direction_failures; q_model = INFINITY; }
                 else if (q_model >= 0) ++st.direction_failures;
                 if (q_model < 0) {
                     // compute_candidate_fbe: pantr.tpp:329-344
-                    for (int i = lane_id(); i < n; i += 32) X[cand * n + i] = X[prox * n + i] + q[i];
-                    __syncwarp();
+                    for (int i = E::first(); i < n; i += E::STEP) X[cand * n + i] = X[prox * n + i] + q[i];
+                    E::sync();
                     eval_psi_grad_psi(cand);
                     double pg = it[prox].gamma, pL = it[prox].L;
-                    __syncwarp();
+                    E::sync();
                     it[cand].gamma = pg; it[cand].L = pL;
-                    __syncwarp();
+                    E::sync();
                     eval_prox_grad_step(cand);
                     if (pp.compute_ratio_using_new_stepsize) { eval_psi_xh(cand); backtrack_qub(cand); }
-                    __syncwarp();
+                    E::sync();
                     // compute_candidate_ratio: pantr.tpp:347-355
                     double phi = fbe(prox), phi_next = fbe(cand);
                     double margin = (1 + fabs(phi)) * pp.TR_tolerance_factor;
@@ -140,16 +140,16 @@
                     // compute_updated_radius: pantr.tpp:358-368,402-403
                     double newD;
                     if (rho >= pp.ratio_threshold_good) {
-                        double a = pp.radius_factor_good * vnorm2(q, n);
+                        double a = pp.radius_factor_good * xnorm2<E>(q, n);
                         newD = a < Delta ? Delta : a; // std::max(a, old)
                     } else if (rho >= pp.ratio_threshold_acceptable)
                         newD = Delta * pp.radius_factor_acceptable;
                     else
-                        newD = pp.radius_factor_rejected * vnorm2(q, n);
+                        newD = pp.radius_factor_rejected * xnorm2<E>(q, n);
                     Delta = fmax(newD, pp.min_radius);
                 }
             }
-            if (tracing && lane_id() == 0) {
+            if (tracing && E::leader()) {
                 int row = *tr.n_rows;
                 if (row < tr.max_rows) {
                     double *o = tr.rows + 11 * row;
@@ -160,12 +160,12 @@
             }
             if (accept_candidate) { // pantr.tpp:411-434
                 if (!pp.compute_ratio_using_new_stepsize) { eval_psi_xh(cand); backtrack_qub(cand); }
-                __syncwarp();
+                E::sync();
                 if (it[prox].gamma != it[cand].gamma && pp.recompute_last_prox_step_after_direction_reset) {
                     double g2 = it[cand].gamma, L2 = it[cand].L;
-                    __syncwarp();
+                    E::sync();
                     it[prox].gamma = g2; it[prox].L = L2;
-                    __syncwarp();
+                    E::sync();
                     eval_prox_grad_step(prox);
                 }
                 int t = curr; curr = cand; cand = t;
@@ -173,12 +173,12 @@
                 if (accelerated_iteration) ++st.accelerated_step_rejected;
                 eval_psi_xh(prox);
                 backtrack_qub(prox);
-                __syncwarp();
+                E::sync();
                 if (it[prox].gamma != it[curr].gamma && pp.recompute_last_prox_step_after_direction_reset) {
                     double g2 = it[prox].gamma, L2 = it[prox].L;
-                    __syncwarp();
+                    E::sync();
                     it[curr].gamma = g2; it[curr].L = L2;
-                    __syncwarp();
+                    E::sync();
                     eval_prox_grad_step(curr);
                 }
                 int t = curr; curr = prox; prox = t;

@@ -124,13 +124,15 @@ def run(argv):
         torch.cuda.get_device_properties(dev), "clock_rate") else 1.965e9
     solve()                                                                    # initial solve, :158
     plant()                                                                    # :160-161
-    runtimes = np.full((B, num_sim), np.nan)
-    wall = np.zeros(num_sim)
-    states = np.zeros((B, nx, num_sim + 1))
-    inputs = np.zeros((record, n, num_sim))
-    first_inputs = np.zeros((B, nu, num_sim))
-    evals = np.zeros(B, dtype=[(k, "i8") for k in STAT_TO_EVAL])
-    iters = np.zeros((B, num_sim), dtype=np.int64)
+    # The closed loop itself is enqueued on the stream in one go: shift -> solve -> record -> plant for
+    # all num_sim steps with no host round trip; per-step results land in device arrays that are read
+    # back once at the end (the reference's loop, mpc-driver.cpp:163-206, per instance).
+    isz = STATS_DTYPE.itemsize
+    stats_all = torch.zeros(num_sim, B * isz, dtype=torch.uint8, device=dev)
+    states_all = torch.empty(num_sim + 1, B, nx, **f64)
+    first_all = torch.empty(num_sim, B, nu, **f64)
+    rec_all = torch.empty(num_sim, record, n, **f64)
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(num_sim)]
     t_begin = time.perf_counter()
     for i in range(num_sim):
         if warm:                                                               # :168-175
@@ -138,19 +140,27 @@ def run(argv):
         else:                                                                  # :192-197
             u.copy_(u_initial)
             y.zero_()
-        st, wall[i] = solve()                                                  # :199
-        t = st["cycles"] / clock_hz
-        runtimes[:, i] = np.where(st["status"] == 1, t, -t)                    # :216-222
-        iters[:, i] = st["inner_iterations"]
-        for k in STAT_TO_EVAL:
-            evals[k] += st[k]
-        states[:, :, i] = x0.cpu().numpy()                                     # :202
-        uh = u.cpu().numpy()
-        inputs[:, :, i] = uh[:record]                                          # :203
-        first_inputs[:, :, i] = uh[:, :nu]
+        evs[i][0].record(stream)
+        solver.solve_device(problem, x0, u, yarg, stats_all[i], stream)        # :199
+        evs[i][1].record(stream)
+        states_all[i].copy_(x0)                                                # :202
+        rec_all[i].copy_(u[:record])                                           # :203
+        first_all[i].copy_(u[:, :nu])
         plant()                                                                # :205
-    states[:, :, num_sim] = x0.cpu().numpy()
+    states_all[num_sim].copy_(x0)
+    torch.cuda.synchronize()
     total = time.perf_counter() - t_begin
+    st_all = stats_all.cpu().numpy().view(STATS_DTYPE).reshape(num_sim, B)
+    wall = np.array([a.elapsed_time(b) * 1e-3 for a, b in evs])
+    t = st_all["cycles"].T / clock_hz
+    runtimes = np.where(st_all["status"].T == 1, t, -t)                        # :216-222
+    iters = st_all["inner_iterations"].T.astype(np.int64)
+    evals = np.zeros(B, dtype=[(k, "i8") for k in STAT_TO_EVAL])
+    for k in STAT_TO_EVAL:
+        evals[k] = st_all[k].sum(axis=0)
+    states = states_all.cpu().numpy().transpose(1, 2, 0).copy()               # [B, nx, num_sim + 1]
+    inputs = rec_all.cpu().numpy().transpose(1, 2, 0).copy()                   # [record, n, num_sim]
+    first_inputs = first_all.cpu().numpy().transpose(1, 2, 0).copy()           # [B, nu, num_sim]
 
     conv = (runtimes > 0).mean()
     print(f"\nsolver:  {solver.get_name()}\nproblem: {name} {horizon} (from {path!r})\n"

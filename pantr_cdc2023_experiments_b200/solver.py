@@ -296,6 +296,11 @@ class ALMSolver:
             C.c_void_p(y_t.data_ptr()) if (y_t is not None and problem.m) else None,
             C.c_void_p(stats_t.data_ptr()), sp))
 
+    def set_exec_mode(self, problem, mode):
+        """'auto' | 'warp' (one warp per instance) | 'thread' (one thread per instance, quadcopters only)."""
+        code = {"auto": 0, "warp": 1, "thread": 2}[mode]
+        _lib.check(_lib.load().pantr_b200_set_exec_mode(self._handle(problem).h, code))
+
     def set_trace(self, problem, instance, max_rows=4096):
         _lib.check(_lib.load().pantr_b200_set_trace(self._handle(problem).h, instance, max_rows))
 

@@ -1,8 +1,8 @@
 #!/bin/bash
-# Parity tests + quick quadcopter throughput.   usage: bash scripts/gpu_quad.sh <tag>
+# usage: gpu_quad.sh <tag> : all GPU tests, then quadcopter quick benches in both execution modes
 TAG=${1:-quad}
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_$TAG.log 2>&1; echo "pytest rc=$?"; tail -25 gpurun_out/pytest_$TAG.log
-timeout 600 python tests/quick_bench_quad.py quadcopter 60 4096 > gpurun_out/quick_quad_$TAG.log 2>&1; cat gpurun_out/quick_quad_$TAG.log
-timeout 600 python tests/quick_bench_quad.py realistic_quadcopter 60 4096 > gpurun_out/quick_rquad_$TAG.log 2>&1; cat gpurun_out/quick_rquad_$TAG.log
-timeout 600 python tests/quick_bench.py 60 16384 > gpurun_out/quick_$TAG.log 2>&1; cat gpurun_out/quick_$TAG.log
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_$TAG.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/pytest_$TAG.log
+for args in "quadcopter 60 1024 warp 0.1" "quadcopter 60 4096 thread 0.1" "quadcopter 60 37888 thread 0.1" "realistic_quadcopter 60 4096 thread 0.1"; do
+  timeout 900 python tests/quick_bench_quad.py $args 2>&1 | tee -a gpurun_out/quick_quad_$TAG.log
+done

@@ -196,3 +196,38 @@ def test_quadcopter_solve_parity(pb, name, pid, N, B):
             np.testing.assert_array_equal(u[b], uo)
             np.testing.assert_array_equal(y[b], yo)
     assert (stats["status"] == 1).all()
+
+
+@pytest.mark.parametrize("name,pid", QUADS)
+@pytest.mark.parametrize("N,B", [(10, 40), (30, 33)])
+def test_quadcopter_thread_per_instance_matches_warp_per_instance_and_oracle(pb, name, pid, N, B):
+    """ThreadExec (32 instances per warp, interleaved vectors) and WarpExec give the same bits."""
+    solver, _ = pb.make_solver(pb.benchmark_options(name))
+    prob = pb.BatchedProblem(name, N)
+    rng = np.random.default_rng(300 + 10 * pid + N)
+    x0 = quad_states(B, rng) * 0.2 + 0.8 * prob.initial_state()
+    x0[0] = prob.initial_state()
+    res = {}
+    for mode in ("warp", "thread"):
+        solver.set_exec_mode(prob, mode)
+        u = np.tile(prob.initial_guess(), (B, 1)); y = np.zeros((B, prob.m))
+        if mode == "thread":
+            solver.set_trace(prob, 0, 8192)
+        st = solver(prob, u, y, x0=x0)
+        res[mode] = (u, y, st, solver.get_trace(prob, 8192) if mode == "thread" else None)
+    solver.set_exec_mode(prob, "auto")
+    uw, yw, sw, _ = res["warp"]; ut, yt, stt, trace = res["thread"]
+    np.testing.assert_array_equal(ut, uw)
+    np.testing.assert_array_equal(yt, yw)
+    for k in sw.dtype.names:
+        if k != "cycles":
+            np.testing.assert_array_equal(stt[k], sw[k], err_msg=k)
+    par = ou.pack_params(solver)
+    for b in (0, B - 1):
+        uo, yo, so, tro = ou.solve(pid, N, par, x0[b], prob.initial_guess(), trace_rows=8192 if b == 0 else 0)
+        assert int(so["status"]) == stt["status"][b]
+        np.testing.assert_array_equal(ut[b], uo)
+        np.testing.assert_array_equal(yt[b], yo)
+        assert int(so["inner_iterations"]) == int(stt["inner_iterations"][b])
+        if b == 0:
+            np.testing.assert_array_equal(tro, trace)

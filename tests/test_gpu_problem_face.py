@@ -103,3 +103,23 @@ def test_null_buffers_are_invalid_argument(pb):
     assert lib.pantr_b200_eval_grad_L_batch(prob._probe.h, 1, None, None, None, None) == -1
     with pytest.raises(ValueError):
         prob.eval_f(np.zeros((2, prob.n + 1)), x0=np.zeros((2, 9)))
+
+
+def test_benchmark_problem_files_hold_the_reference_model_data(pb, tmp_path):
+    """<name>_ss2p_<N>.csv / .guess.csv as problems/generate_problem.py writes them, from the device library's model."""
+    from pantr_cdc2023_experiments_b200 import problem_data as pd
+    prob = pb.BatchedProblem("quadcopter", 4)
+    base = pd.write_benchmark_problem_files(prob, str(tmp_path))
+    assert base.endswith("quadcopter_ss2p_4")
+    d = pd.read_problem_data(base + ".csv", n=16, m=20, p=9)
+    np.testing.assert_array_equal(d["C"][0], np.tile([0, -0.1, -0.1, -0.1], 4))       # quadcopter.py:56-59, ss.py:28-29
+    np.testing.assert_array_equal(d["C"][1], np.tile([9.81 * 5, 0.1, 0.1, 0.1], 4))
+    np.testing.assert_array_equal(d["D"][0], np.tile([-np.pi / 2, -np.pi / 2, np.cos(1.1 / 2), -np.inf], 5))
+    np.testing.assert_array_equal(d["D"][1], np.tile([np.pi / 2, np.pi / 2, np.inf, 0], 5))
+    np.testing.assert_array_equal(d["param"], [-0.2, -0.25, 0.5, 0, 0, 0, 0, 0, 0])   # quadcopter.py:78-83
+    g, split = pd.read_guess(base + ".guess.csv")
+    np.testing.assert_array_equal(g, np.tile([9.81, 0, 0, 0], 4)); assert split == 0  # quadcopter.py:112
+    hc = pb.BatchedProblem("hanging_chain", 3)
+    d = pd.read_problem_data(pd.write_benchmark_problem_files(hc, str(tmp_path)) + ".csv", n=9, m=0, p=57)
+    np.testing.assert_array_equal(d["C"][0], -np.ones(9)); assert d["D"][0].size == 0
+    np.testing.assert_array_equal(d["param"][0:30:3], (np.arange(10) + 1) / 10)       # hanging_chain.py:92-96
