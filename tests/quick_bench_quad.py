@@ -10,7 +10,8 @@ N = int(sys.argv[2]) if len(sys.argv) > 2 else 60
 B = int(sys.argv[3]) if len(sys.argv) > 3 else 4096
 mode = sys.argv[4] if len(sys.argv) > 4 else "auto"
 scale = float(sys.argv[5]) if len(sys.argv) > 5 else 0.2
-solver, _ = pb.make_solver(pb.benchmark_options(name))
+extra = sys.argv[6:]  # option overrides, e.g. alm.max_iter=10 solver.max_iter=100 (bounds the tail)
+solver, _ = pb.make_solver(pb.benchmark_options(name) + extra)
 prob = pb.BatchedProblem(name, N)
 solver.set_exec_mode(prob, mode)
 rng = np.random.default_rng(0)
@@ -23,4 +24,5 @@ for rep in range(2):
     it = st['inner_iterations']
     print(f"{name} {mode} scale {scale} cold N={N} B={B}: {t:.3f}s  {B/t:.1f} solves/s  converged {np.mean(st['status']==1):.3f} "
           f"outer mean {st['outer_iterations'].mean():.1f} inner mean {it.mean():.1f} p50 {np.median(it):.0f} p99 {np.percentile(it, 99):.0f} max {it.max()} "
-          f"hvp mean {st['ev_hess_psi_prod'].mean():.1f} -> {st['ev_hess_psi_prod'].sum()/t/1e6:.2f} M hvp/s", flush=True)
+          f"hvp mean {st['ev_hess_psi_prod'].mean():.1f} -> {st['ev_hess_psi_prod'].sum()/t/1e6:.2f} M hvp/s ; "
+          f"per-slot {st['ev_hess_psi_prod'].sum()/(st['cycles'].sum()/1.965e9):.0f} hvp/s while busy", flush=True)
