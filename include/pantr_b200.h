@@ -213,6 +213,13 @@ int pantr_b200_simulate_dynamics_batch_device(pantr_b200_solver *s, int64_t B, c
 int pantr_b200_shift_warm_start_device(pantr_b200_solver *s, int64_t B, double *d_u, double *d_y,
                                        void *stream);
 
+/* Scheduling hint for the next solves (warp-per-instance path): d_order is a DEVICE array with a permutation
+ * of 0..B-1; resident blocks take instances in that order instead of by index.  In closed-loop MPC the
+ * previous step's per-instance cost (stats[b].cycles) predicts the next one, and starting the expensive
+ * instances first shortens the tail of the launch.  Results do not depend on the order.  NULL = by index.
+ * The array is caller-owned and must stay valid (and of length >= B) while it is set. */
+int pantr_b200_set_order_device(pantr_b200_solver *s, const int32_t *d_order);
+
 /* How instances map onto the GPU for the next solves: 0 = automatic (default), 1 = one warp per instance,
  * 2 = one thread per instance (32 per warp; quadcopter models only, ignored for the hanging chain).
  * Automatic picks 2 for the quadcopters when B >= 256.  Results are bit-identical in both mappings. */

@@ -93,7 +93,7 @@
                     eps_ = fmax(rho * eps_old, a.tolerance);
                     ++penalty_reduced;
                 } else {
-                    for (int j = E::first(); j < m; j += E::STEP) S[j] *= a.initial_penalty_lower;
+                    for (int j = E::first(); j < m; j += E::STEP) S[j] = S[j] * a.initial_penalty_lower;
                     E::sync();
                     eps_ *= a.initial_tolerance_increase;
                     ++initial_penalty_reduced;

@@ -34,6 +34,7 @@ struct KernelArgs {
     unsigned long long *counter;
     Trace trace;
     int smem_set; // which solver vectors live in dynamic shared memory (Pantr::smem_bytes)
+    const int *order; // optional: queue ticket -> instance index (longest-expected-first scheduling)
 };
 
 // ---- the solve kernel: ALMSolver::operator() for every instance of the batch ----
@@ -48,6 +49,7 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
         if (lane_id() == 0) b = atomicAdd(A.counter, 1ULL);
         b = __shfl_sync(FULL, b, 0);
         if (b >= (unsigned long long)A.B) break;
+        if (A.order) b = (unsigned long long)A.order[b];
         long long t0 = clock64();
         Model mdl;
         mdl.init(A.N, A.x0 + b * A.nx, ws);
@@ -69,8 +71,11 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
 
 // ---- thread-per-instance variant (ThreadExec, exec_policy.cuh): 32 instances per warp, vectors
 // interleaved across the warp.  For the small-state models whose sweeps are sequential chains. ----
+#ifndef PANTR_THREAD_MIN_BLOCKS
+#define PANTR_THREAD_MIN_BLOCKS 8 // resident warps per SM the thread-per-instance kernel is compiled for
+#endif
 template <class Model>
-__global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel_thread(const __grid_constant__ SolverParams P,
+__global__ void __launch_bounds__(32, PANTR_THREAD_MIN_BLOCKS) solve_kernel_thread(const __grid_constant__ SolverParams P,
                                                                              const __grid_constant__ KernelArgs A) {
     IterScalars it[3];
     const int lane = lane_id();

@@ -296,6 +296,12 @@ class ALMSolver:
             C.c_void_p(y_t.data_ptr()) if (y_t is not None and problem.m) else None,
             C.c_void_p(stats_t.data_ptr()), sp))
 
+    def set_order(self, problem, order_t):
+        """Scheduling hint: int32 CUDA tensor with a permutation of range(B) (kept alive here), or None."""
+        self._order = order_t
+        ptr = None if order_t is None else C.c_void_p(order_t.data_ptr())
+        _lib.check(_lib.load().pantr_b200_set_order_device(self._handle(problem).h, ptr))
+
     def set_exec_mode(self, problem, mode):
         """'auto' | 'warp' (one warp per instance) | 'thread' (one thread per instance, quadcopters only)."""
         code = {"auto": 0, "warp": 1, "thread": 2}[mode]

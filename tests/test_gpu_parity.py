@@ -231,3 +231,21 @@ def test_quadcopter_thread_per_instance_matches_warp_per_instance_and_oracle(pb,
         assert int(so["inner_iterations"]) == int(stt["inner_iterations"][b])
         if b == 0:
             np.testing.assert_array_equal(tro, trace)
+
+
+def test_instance_order_hint_does_not_change_results(pb):
+    import torch
+    N, B = 12, 50
+    solver, _ = pb.make_solver(pb.benchmark_options("hanging_chain"))
+    prob = pb.BatchedProblem("hanging_chain", N)
+    rng = np.random.default_rng(5)
+    x0 = disturbed_states(prob, B, rng)
+    u0 = np.zeros((B, prob.n)); st0 = solver(prob, u0, None, x0=x0)
+    order = torch.from_numpy(rng.permutation(B).astype(np.int32)).cuda()
+    solver.set_order(prob, order)
+    u1 = np.zeros((B, prob.n)); st1 = solver(prob, u1, None, x0=x0)
+    solver.set_order(prob, None)
+    np.testing.assert_array_equal(u1, u0)
+    for k in st0.dtype.names:
+        if k != "cycles":
+            np.testing.assert_array_equal(st1[k], st0[k], err_msg=k)
