@@ -40,7 +40,7 @@ def parse_args():
     ap.add_argument("--horizon", type=int, default=HORIZON)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--order", default="history", choices=["history", "index"],
+    ap.add_argument("--order", default="index", choices=["history", "index"],
                     help="instance scheduling inside the launch: by the previous (cold) solve's cost, longest first, or by index")
     return ap.parse_args()
 
