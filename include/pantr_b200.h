@@ -221,8 +221,11 @@ int pantr_b200_shift_warm_start_device(pantr_b200_solver *s, int64_t B, double *
 int pantr_b200_set_order_device(pantr_b200_solver *s, const int32_t *d_order);
 
 /* How instances map onto the GPU for the next solves: 0 = automatic (default), 1 = one warp per instance,
- * 2 = one thread per instance (32 per warp; quadcopter models only, ignored for the hanging chain).
- * Automatic picks 2 for the quadcopters when B >= 256.  Results are bit-identical in both mappings. */
+ * whole solves handed out by a queue, 2 = one thread per instance (32 per warp; quadcopter models only),
+ * 3 = one warp per instance, PANTR *iterations* handed out by a queue (models without general constraints,
+ * i.e. the hanging chain; per-instance state lives in HBM between iterations so that all instances advance at the
+ * same rate).  Automatic picks 2 for the quadcopters when B >= 256, else 1.  Modes that do not apply to the
+ * model fall back to 1.  Results are bit-identical in all mappings. */
 int pantr_b200_set_exec_mode(pantr_b200_solver *s, int mode);
 
 /* Optional per-iteration trace of one instance of the next solve_batch call (debug / parity):

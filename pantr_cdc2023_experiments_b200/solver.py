@@ -303,8 +303,9 @@ class ALMSolver:
         _lib.check(_lib.load().pantr_b200_set_order_device(self._handle(problem).h, ptr))
 
     def set_exec_mode(self, problem, mode):
-        """'auto' | 'warp' (one warp per instance) | 'thread' (one thread per instance, quadcopters only)."""
-        code = {"auto": 0, "warp": 1, "thread": 2}[mode]
+        """'auto' | 'warp' (one warp per instance, whole solves) | 'thread' (one thread per instance, quadcopters
+        only) | 'sliced' (one warp per instance, PANTR iterations handed out one by one; hanging chain only)."""
+        code = {"auto": 0, "warp": 1, "thread": 2, "sliced": 3}[mode]
         _lib.check(_lib.load().pantr_b200_set_exec_mode(self._handle(problem).h, code))
 
     def set_trace(self, problem, instance, max_rows=4096):

@@ -6,6 +6,7 @@ N = int(sys.argv[1]) if len(sys.argv) > 1 else 60
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 2048
 solver, _ = pb.make_solver(pb.benchmark_options("hanging_chain"))
 prob = pb.BatchedProblem("hanging_chain", N)
+solver.set_exec_mode(prob, os.environ.get("PANTR_EXEC_MODE", "auto"))
 rng = np.random.default_rng(0)
 x0 = np.tile(prob.initial_state(), (B, 1))
 for _ in range(5):

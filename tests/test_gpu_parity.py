@@ -249,3 +249,29 @@ def test_instance_order_hint_does_not_change_results(pb):
     for k in st0.dtype.names:
         if k != "cycles":
             np.testing.assert_array_equal(st1[k], st0[k], err_msg=k)
+
+
+@pytest.mark.parametrize("N,B", [(12, 5000), (30, 4800)])
+def test_iteration_sliced_scheduling_matches_whole_solve_scheduling(pb, N, B):
+    """exec mode 'sliced' (PANTR iterations handed out through the device ring, per-instance state in HBM)
+    gives the same bits as mode 'warp' (whole solves), including all counters; instance 0 also vs the oracle."""
+    solver, _ = pb.make_solver(pb.benchmark_options("hanging_chain"))
+    prob = pb.BatchedProblem("hanging_chain", N)
+    rng = np.random.default_rng(N)
+    x0 = disturbed_states(prob, B, rng)
+    res = {}
+    for mode in ("warp", "sliced"):
+        solver.set_exec_mode(prob, mode)
+        u = np.zeros((B, prob.n))
+        res[mode] = (u, solver(prob, u, None, x0=x0))
+    solver.set_exec_mode(prob, "auto")
+    for mode in ("sliced",):
+        np.testing.assert_array_equal(res[mode][0], res["warp"][0])
+        for k in res["warp"][1].dtype.names:
+            if k != "cycles":
+                np.testing.assert_array_equal(res[mode][1][k], res["warp"][1][k], err_msg=k)
+    assert (res["sliced"][1]["status"] == 1).all()
+    par = ou.pack_params(solver)
+    uo, _, so, _ = ou.solve(0, N, par, x0[0], np.zeros(prob.n))
+    np.testing.assert_array_equal(res["sliced"][0][0], uo)
+    assert int(so["inner_iterations"]) == res["sliced"][1]["inner_iterations"][0]
