@@ -322,9 +322,10 @@ def run_b200(args):
     launches = solver.kernel_launches(prob) - launches0
     kernel_ms = float(np.mean([a.elapsed_time(b) for a, b in kev]))
     stats = stats_t.cpu().numpy().view(pb.STATS_DTYPE).copy()
-    clock_hz = 1e6 * (clocks["sm_mhz"] if (clocks and clocks.get("sm_mhz")) else 1965.0)
     grid_now = solver.grid_size(prob)
-    slot_util = float(stats["cycles"].astype("f8").sum() / (kernel_ms * 1e-3 * clock_hz * min(grid_now, B)))
+    busy_us = float(stats["elapsed_us"].astype("f8").sum())                 # globaltimer, per instance
+    slot_util = busy_us / (kernel_ms * 1e3 * min(grid_now, B))
+    sm_mhz_in_kernel = float(stats["cycles"].astype("f8").sum() / max(busy_us, 1.0))   # clock64 / globaltimer
     conv_local = int((stats["status"] == 1).sum())
     conv_total = sum_over_ranks(conv_local)
     value = conv_total * args.steps / (total_ms * 1e-3)
@@ -438,7 +439,7 @@ def run_b200(args):
             "e2e": {"value": e2e_value, "unit": "solves/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": e2e_steps, "bitwise_equal_to_device_path": same_as_device},
             "gpu_launches": int(launches), "grid": solver.grid_size(prob),
-            "scheduling": {"order": args.order, "slot_utilisation": slot_util,
+            "scheduling": {"order": args.order, "slot_utilisation": slot_util, "sm_mhz_in_kernel": sm_mhz_in_kernel,
                            "kernel_ms_other_order": other_ms,
                            "cycles_mean": float(stats["cycles"].mean()), "cycles_max": float(stats["cycles"].max())},
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "parity_check": parity,

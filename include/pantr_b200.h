@@ -99,8 +99,8 @@ typedef struct pantr_b200_stats {
     double eps, delta, norm_penalty, final_gamma, final_psi, final_h, final_fbe;
     uint32_t ev_proj_multipliers, ev_prox_grad_step, ev_inactive_indices_res_lna, ev_grad_L,
         ev_hess_psi_prod, ev_psi, ev_grad_psi, ev_psi_grad_psi, ev_f, ev_g;
-    uint32_t cg_iterations, reserved;
-    uint64_t cycles; /* SM clock cycles this instance occupied its warp */
+    uint32_t cg_iterations, elapsed_us; /* elapsed_us: wall time (globaltimer) this instance occupied its warp / thread */
+    uint64_t cycles; /* SM clock cycles over the same interval: cycles / elapsed_us = the SM clock in MHz under load */
 } pantr_b200_stats;
 
 typedef struct pantr_b200_solver pantr_b200_solver;

@@ -55,7 +55,7 @@ class StatsC(C.Structure):
         (k, C.c_uint32) for k in (
         "ev_proj_multipliers", "ev_prox_grad_step", "ev_inactive_indices_res_lna", "ev_grad_L",
         "ev_hess_psi_prod", "ev_psi", "ev_grad_psi", "ev_psi_grad_psi", "ev_f", "ev_g",
-        "cg_iterations", "reserved")] + [("cycles", C.c_uint64)]
+        "cg_iterations", "elapsed_us")] + [("cycles", C.c_uint64)]
 
 
 # every symbol include/pantr_b200.h declares

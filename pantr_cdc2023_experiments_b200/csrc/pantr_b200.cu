@@ -23,6 +23,12 @@ int fail(int code, const std::string &msg) { g_last_error = msg; return code; }
             return fail(PANTR_B200_CUDA_ERROR, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 struct KernelArgs {
     int N, n, m, nx;
     long long B;
@@ -51,6 +57,7 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
         if (b >= (unsigned long long)A.B) break;
         if (A.order) b = (unsigned long long)A.order[b];
         long long t0 = clock64();
+        const unsigned long long g0 = globaltimer_ns();
         Model mdl;
         mdl.init(A.N, A.x0 + b * A.nx, ws);
         Pantr<Model> S(mdl, P, it, A.n, A.m, ws + Model::traj_doubles(A.N), dyn_smem, A.smem_set);
@@ -64,6 +71,7 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
         __syncwarp();
         for (int i = lane_id(); i < A.m; i += 32) A.y[b * A.m + i] = S.y[i];
         S.st.cycles = (unsigned long long)(clock64() - t0);
+        S.st.elapsed_us = (unsigned)((globaltimer_ns() - g0) / 1000);
         if (lane_id() == 0) A.stats[b] = S.st;
         __syncwarp();
     }
@@ -77,10 +85,10 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
 // Here the unit of work is ONE PANTR iteration: the iterate slots (x, x_hat, grad psi, p: 12 n doubles) and the
 // loop scalars of every INSTANCE live in global memory, a resident warp pops an instance from a multi-producer /
 // multi-consumer ring, advances it by `chunk` iterations and pushes it back, so all instances progress
-// at the same rate.  Same arithmetic, same results.  MEASURED: no faster than whole solves (warm 0.393 s vs
-// 0.396 s for 16384 instances): round-robin finishes the many short instances together and still leaves the
-// few long ones to run out serially at the end; it takes a remaining-work predictor (a priority on this
-// ring) to beat that, which is what this kernel is the vehicle for.  Selected with exec mode 3 only.
+// at the same rate; instances predicted to have much work left go through a second ring that is served first.
+// Same arithmetic, same results.  MEASURED (16384 warm instances): whole solves 396 ms, round-robin 393-408 ms,
+// with the priority ring 419-434 ms -- no gain: when an SM's slots run dry its remaining warps speed up, so the
+// idle slot-time of the whole-solve kernel is not really lost.  Kept behind exec mode 3.
 struct InstState {
     int started, pad;
     IterScalars it[3];
@@ -89,10 +97,14 @@ struct InstState {
     int s_curr, s_prox, s_cand, s_always, s_errz;
     unsigned s_k, s_no_progress, pad2;
 };
-struct SliceQueue {
-    unsigned long long *head, *tail, *done, *flag; // flag[slot] = ticket + 1 while the slot holds an item, else 0
+struct SliceRing {
+    unsigned long long *head, *tail, *flag; // flag[slot] = ticket + 1 while the slot holds an item, else 0
     int *ring;
     unsigned cap;
+};
+struct SliceQueue {
+    SliceRing urgent, normal; // instances predicted to have much work left are served first
+    unsigned long long *done;
 };
 __device__ __forceinline__ unsigned long long ld_acquire(const unsigned long long *p) {
     unsigned long long v;
@@ -102,30 +114,47 @@ __device__ __forceinline__ unsigned long long ld_acquire(const unsigned long lon
 __device__ __forceinline__ void st_release(unsigned long long *p, unsigned long long v) {
     asm volatile("st.release.gpu.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ long long queue_pop(const SliceQueue &Q, long long B) {
-    const unsigned long long h = atomicAdd(Q.head, 1ULL);
-    const unsigned slot = (unsigned)(h % Q.cap);
+/// non-blocking: claims a ticket only if a push has already reserved it (its item is published at once)
+__device__ long long ring_try_pop(const SliceRing &R) {
+    unsigned long long h;
     for (;;) {
-        if (ld_acquire(Q.flag + slot) == h + 1) break;
+        h = ld_acquire(R.head);
+        if (h >= ld_acquire(R.tail)) return -1;
+        if (atomicCAS(R.head, h, h + 1) == h) break;
+    }
+    const unsigned slot = (unsigned)(h % R.cap);
+    while (ld_acquire(R.flag + slot) != h + 1) __nanosleep(64);
+    const int id = R.ring[slot];
+    st_release(R.flag + slot, 0ULL);
+    return id;
+}
+__device__ void ring_push(const SliceRing &R, int id) {
+    const unsigned long long t = atomicAdd(R.tail, 1ULL);
+    const unsigned slot = (unsigned)(t % R.cap);
+    while (ld_acquire(R.flag + slot) != 0ULL) __nanosleep(64);
+    R.ring[slot] = id;
+    st_release(R.flag + slot, t + 1);
+}
+__device__ long long queue_pop(const SliceQueue &Q, long long B) {
+    for (;;) {
+        long long id = ring_try_pop(Q.urgent);
+        if (id >= 0) return id;
+        id = ring_try_pop(Q.normal);
+        if (id >= 0) return id;
         if (ld_acquire(Q.done) >= (unsigned long long)B) return -1; // every instance has finished: no more pushes
         __nanosleep(256);
     }
-    const int id = Q.ring[slot];
-    st_release(Q.flag + slot, 0ULL);
-    return id;
-}
-__device__ void queue_push(const SliceQueue &Q, int id) {
-    const unsigned long long t = atomicAdd(Q.tail, 1ULL);
-    const unsigned slot = (unsigned)(t % Q.cap);
-    while (ld_acquire(Q.flag + slot) != 0ULL) __nanosleep(128);
-    Q.ring[slot] = id;
-    st_release(Q.flag + slot, t + 1);
 }
 __global__ void queue_init_kernel(SliceQueue Q, long long B) {
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)Q.cap; i += (long long)gridDim.x * blockDim.x) {
-        Q.ring[i] = (int)(i < B ? i : 0);
-        Q.flag[i] = i < B ? (unsigned long long)i + 1 : 0ULL;
-        if (i == 0) { *Q.head = 0; *Q.tail = (unsigned long long)B; *Q.done = 0; }
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)Q.normal.cap; i += (long long)gridDim.x * blockDim.x) {
+        Q.normal.ring[i] = (int)(i < B ? i : 0);
+        Q.normal.flag[i] = i < B ? (unsigned long long)i + 1 : 0ULL;
+        Q.urgent.ring[i] = 0;
+        Q.urgent.flag[i] = 0ULL;
+        if (i == 0) {
+            *Q.normal.head = 0; *Q.normal.tail = (unsigned long long)B; *Q.urgent.head = 0; *Q.urgent.tail = 0;
+            *Q.done = 0;
+        }
     }
 }
 
@@ -133,7 +162,7 @@ template <class Model>
 __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel_sliced(const __grid_constant__ SolverParams P,
                                                                              const __grid_constant__ KernelArgs A,
                                                                              const SliceQueue Q, double *inst_vec,
-                                                                             InstState *inst_state, int chunk) {
+                                                                             InstState *inst_state, int chunk, int urgent_cg) {
     static_assert(Model::NC == 0, "the sliced kernel covers the m = 0 branch of ALMSolver (alm.tpp:29-52)");
     __shared__ IterScalars it[3];
     extern __shared__ __align__(16) double dyn_smem[];
@@ -147,6 +176,7 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel_sliced(con
         if (b < 0) break;
         __threadfence(); // acquire side for every lane: the instance's state was written by another SM
         long long t0 = clock64();
+        const unsigned long long g0 = globaltimer_ns();
         InstState &IS = inst_state[b];
         Model mdl;
         mdl.init(A.N, A.x0 + b * A.nx, ws);
@@ -175,6 +205,7 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel_sliced(con
         for (int c = 0; c < chunk && !done; ++c) done = S.inner_iterate(s, res, nullptr);
         __syncwarp();
         S.st.cycles += (unsigned long long)(clock64() - t0);
+        S.st.elapsed_us += (unsigned)((globaltimer_ns() - g0) / 1000);
         if (done) { // alm.tpp:29-52
             S.accumulate(res);
             S.st.eps = res.eps; S.st.delta = 0; S.st.norm_penalty = 0; S.st.outer_iterations = 1;
@@ -194,7 +225,10 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel_sliced(con
             }
             __threadfence(); // release side: the iterate slots written by all lanes, the scalars by lane 0
             __syncwarp();
-            if (lane == 0) queue_push(Q, (int)b);
+            // Remaining-work predictor (oracle study): a short CG run in the second PANTR iteration
+            // (<= 5 iterations) precedes 84 % of the >12-iteration solves; anything alive after 6 is long too.
+            const bool urgent = urgent_cg >= 0 && ((s.k >= 2 && S.cg_last <= (unsigned)urgent_cg) || s.k >= 6);
+            if (lane == 0) ring_push(urgent ? Q.urgent : Q.normal, (int)b);
         }
         __syncwarp();
     }
@@ -217,6 +251,7 @@ __global__ void __launch_bounds__(32, PANTR_THREAD_MIN_BLOCKS) solve_kernel_thre
         const long long b = (long long)base + lane;
         if (b < A.B) {
             long long t0 = clock64();
+            const unsigned long long g0 = globaltimer_ns();
             Model mdl;
             mdl.init(A.N, A.x0 + b * A.nx, ws);
             Pantr<Model, ThreadExec> S(mdl, P, it, A.n, A.m, ws + Model::traj_doubles(A.N));
@@ -229,6 +264,7 @@ __global__ void __launch_bounds__(32, PANTR_THREAD_MIN_BLOCKS) solve_kernel_thre
             for (int i = 0; i < A.n; ++i) A.u[b * A.n + i] = S.x[i];
             for (int i = 0; i < A.m; ++i) A.y[b * A.m + i] = S.y[i];
             S.st.cycles = (unsigned long long)(clock64() - t0);
+            S.st.elapsed_us = (unsigned)((globaltimer_ns() - g0) / 1000);
             A.stats[b] = S.st;
         }
         __syncwarp();

@@ -22,4 +22,6 @@ xn = prob.simulate_dynamics(x0, u[:, :3])
 uw = np.concatenate([u[:, 3:], u[:, -3:]], axis=1).copy()
 t = time.time(); st = solver(prob, uw, None, x0=xn); t = time.time() - t
 print(f"warm N={N} B={B}: {t:.3f}s  {B/t:.1f} solves/s  converged {np.mean(st['status']==1):.3f} "
-      f"iters mean {st['inner_iterations'].mean():.1f} hvp mean {st['ev_hess_psi_prod'].mean():.1f}")
+      f"iters mean {st['inner_iterations'].mean():.1f} hvp mean {st['ev_hess_psi_prod'].mean():.1f} "
+      f"SM clock in kernel {st['cycles'].sum()/max(1,st['elapsed_us'].sum()):.0f} MHz, slot busy "
+      f"{st['elapsed_us'].sum()/1e6/(t*min(B, solver.grid_size(prob))):.3f} of host-timed wall")
