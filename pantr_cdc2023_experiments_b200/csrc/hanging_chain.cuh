@@ -197,6 +197,29 @@ __device__ __forceinline__ void stage_fetch(const Lane &L, double *buf, const do
     if (l < 20) cp_async16(buf + SCSTEP + 2 * l, iw + 2 * l);
     (void)L;
 }
+// ---- PANTR_HC_VARIANT >= 1: the Hessian-vector product reads the stage points' link vectors from a cache ----
+// dic  N x 160: per RK4 step the 4 x 30 lane values of `dist` at the stage points followed by the 4 x 10
+// values of 1/|dist| (a copy of the step's iwc block, so that one contiguous block feeds both sweeps of
+// the product).  Written by the adjoint sweep (depends on u only, like adjc); with it the product does
+// not rebuild the stage points (no state trajectory reads, no k_j chain, 8 shuffles fewer per stage).
+#ifndef PANTR_HC_VARIANT
+#define PANTR_HC_VARIANT 3
+#endif
+constexpr int DSTEP = 4 * NL + 4 * NLINK; // 160 doubles
+__device__ __forceinline__ void link_cached(double dist, double iw, Link &ld, double &iw2) {
+    ld.dist = dist;
+    ld.c    = hcf::spring_c(iw);
+    iw2     = iw * iw;
+    ld.e    = hcf::spring_e(iw, iw2);
+}
+/// 160 doubles global -> shared with cp.async (80 chunks of 16 bytes)
+__device__ __forceinline__ void fetch160(double *buf, const double *g) {
+    const int l = lane_id();
+    cp_async16(buf + 2 * l, g + 2 * l);
+    cp_async16(buf + 2 * (l + 32), g + 2 * (l + 32));
+    if (l < 16) cp_async16(buf + 2 * (l + 64), g + 2 * (l + 64));
+}
+__device__ __forceinline__ void cp_async_wait_1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 __device__ __forceinline__ void stages_cached(const Lane &L, double X, double V, double ud, const IW &iw,
                                               Link (&ld)[4], double (&iw2)[4]) {
     double Vu = L.hasV ? V : ud, kX, kV;
@@ -240,7 +263,8 @@ __device__ __noinline__ double rollout(int N, const double *x0, const double *u,
 // Also fills adjc (N x 4 x 40): Fbar (lane) and dist . Fbar (link) of every stage, which depend on
 // u only and are reused by every Hessian-vector product at this u (~30 per gradient).
 __device__ __noinline__ void adjoint(int N, const double *u, const double *traj, const double *iwc,
-                                     double *grad, double *adjc) {
+                                     double *grad, double *adjc, double *dic) {
+    __builtin_assume(__isGlobal(dic));
     __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(traj)); __builtin_assume(__isGlobal(iwc));
     __builtin_assume(__isGlobal(adjc)); // grad may be shared memory
     const Lane L;
@@ -259,6 +283,19 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
         if (k > 0) { load_state(L, traj, k - 1, Xp, Vp); up = load_u(L, u, k - 1); iwp = load_iw(L, iwc, k - 1); }
         Link ld[4]; double iw2[4];
         stages_cached(L, X, V, ud, iw, ld, iw2);
+#if PANTR_HC_VARIANT >= 1
+        {
+            double *dc = dic + k * DSTEP;
+            if (L.active) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) __stcg(dc + j * NL + L.l, ld[j].dist);
+                if (L.l == L.base) {
+                    __stcg(dc + 4 * NL + L.link, iw.i0); __stcg(dc + 4 * NL + NLINK + L.link, iw.i1);
+                    __stcg(dc + 4 * NL + 2 * NLINK + L.link, iw.i2); __stcg(dc + 4 * NL + 3 * NLINK + L.link, iw.i3);
+                }
+            }
+        }
+#endif
         double wX, wV, aX, aV, sX, sV, Fb, dt;
         wX = h6 * lX; wV = h6 * lV;
         double *ac = adjc + k * SCSTEP;
@@ -290,8 +327,9 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
 // Hv = hess f(u) v by forward-over-adjoint (the exact Hessian-vector product that
 // casadi_generator/__init__.py:181-189 defines as hess_psi_prod; with m = 0, psi = f).
 // traj / iwc hold the rollout of `u`; dtraj is scratch for the tangent trajectory.
+#if PANTR_HC_VARIANT == 0
 __device__ __noinline__ void hvp(int N, const double *u, const double *v, const double *traj, double *dtraj,
-                                 const double *iwc, const double *adjc, double *Hv) {
+                                 const double *iwc, const double *adjc, const double *, double *Hv) {
     __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(traj)); // v, Hv may be shared memory
     __builtin_assume(__isGlobal(dtraj)); __builtin_assume(__isGlobal(iwc));
     __builtin_assume(__isGlobal(adjc));
@@ -397,6 +435,232 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
         X = Xp; V = Vp; dX = dXp; dV = dVp; ud = up; vd = vp;
     }
 }
+#else
+// Variants 1 and 2: the stage points' link vectors come from dic, so neither sweep touches the state
+// trajectory.  Variant 2 software-pipelines the reverse sweep: the tangent stage chain (jvp) of step
+// k-1 depends on dtraj / dic only, so it is issued alongside the second-order adjoint chain (hvjp) of
+// step k — two independent dependency chains per warp instead of one (the kernel is bound by
+// dependent-issue latency at 4 warps per scheduler).  Same operations on the same operands as variant 0.
+/// v_k on lanes 27..29 by an unpredicated load (the other lanes read v[3k], which nothing consumes: a
+/// predicated load followed by a zeroing move exposed the whole load latency once per step,
+/// 10 % of all warp samples in the first capture of this variant)
+__device__ __forceinline__ double load_v(const Lane &L, const double *v, int k) {
+    return v[NU * k + (L.isEnd ? L.l - NVL : 0)];
+}
+// Tangent trajectory rows are padded to 58 doubles (16-byte aligned) so that the reverse sweep can
+// stage them with 16-byte cp.async like the other per-step blocks.
+constexpr int DTS = NX + 1;
+__device__ __forceinline__ void dt_store(const Lane &L, double *t, int k, double X, double V) {
+    double *s = t + k * DTS;
+    if (L.active) __stcg(s + L.l, X);
+    if (L.hasV) __stcg(s + NL + L.l, V);
+}
+__device__ __forceinline__ void dt_load(const Lane &L, const double *t, int k, double &X, double &V) {
+    const double *s = t + k * DTS;
+    X = L.active ? __ldcg(s + L.l) : 0.0;
+    V = L.hasV ? __ldcg(s + NL + L.l) : 0.0;
+}
+__device__ __forceinline__ void fetch_row(double *buf, const double *g) { // 58 doubles = 29 chunks
+    const int l = lane_id();
+    if (l < DTS / 2) cp_async16(buf + 2 * l, g + 2 * l);
+}
+struct Tan { double ddist[4], dd[4]; };
+__device__ __forceinline__ void jvp_chain(const Lane &L, const double *db, double dX, double dV, double vd,
+                                          Tan &T, double (&kX)[4], double (&kV)[4]) {
+    Link ld; double iw2;
+    link_cached(L.active ? db[L.l] : 0.0, db[4 * NL + L.link], ld, iw2);
+    jvp(L, ld, dX, L.hasV ? dV : vd, kX[0], kV[0], T.ddist[0], T.dd[0]);
+    double sX = hcf::axpy(hh, kX[0], dX), sV = hcf::axpy(hh, kV[0], dV);
+    link_cached(L.active ? db[NL + L.l] : 0.0, db[4 * NL + NLINK + L.link], ld, iw2);
+    jvp(L, ld, sX, L.hasV ? sV : vd, kX[1], kV[1], T.ddist[1], T.dd[1]);
+    sX = hcf::axpy(hh, kX[1], dX); sV = hcf::axpy(hh, kV[1], dV);
+    link_cached(L.active ? db[2 * NL + L.l] : 0.0, db[4 * NL + 2 * NLINK + L.link], ld, iw2);
+    jvp(L, ld, sX, L.hasV ? sV : vd, kX[2], kV[2], T.ddist[2], T.dd[2]);
+    sX = hcf::axpy(h, kX[2], dX); sV = hcf::axpy(h, kV[2], dV);
+    link_cached(L.active ? db[3 * NL + L.l] : 0.0, db[4 * NL + 3 * NLINK + L.link], ld, iw2);
+    jvp(L, ld, sX, L.hasV ? sV : vd, kX[3], kV[3], T.ddist[3], T.dd[3]);
+}
+/// second-order adjoint chain of one RK4 step; db = the step's dic block, ab = its adjc block (shared memory)
+__device__ __forceinline__ void hvjp_chain(const Lane &L, const double *db, const double *ab, const Tan &T,
+                                           double mX, double mV, double &tX, double &tV) {
+    Link ld; double iw2, dwX, dwV, bX, bV;
+    // stage 4
+    link_cached(L.active ? db[3 * NL + L.l] : 0.0, db[4 * NL + 3 * NLINK + L.link], ld, iw2);
+    dwX = h6 * mX; dwV = h6 * mV;
+    hvjp(L, ld, iw2, L.active ? ab[3 * SC + L.l] : 0.0, ab[3 * SC + NL + L.link], T.ddist[3], T.dd[3], dwX, dwV, bX, bV);
+    tX = mX + bX; tV = mV + bV;
+    // stage 3
+    link_cached(L.active ? db[2 * NL + L.l] : 0.0, db[4 * NL + 2 * NLINK + L.link], ld, iw2);
+    dwX = hcf::lin2(h3, mX, h, bX); dwV = hcf::lin2(h3, mV, h, bV);
+    hvjp(L, ld, iw2, L.active ? ab[2 * SC + L.l] : 0.0, ab[2 * SC + NL + L.link], T.ddist[2], T.dd[2], dwX, dwV, bX, bV);
+    tX = tX + bX; tV = tV + bV;
+    // stage 2
+    link_cached(L.active ? db[NL + L.l] : 0.0, db[4 * NL + NLINK + L.link], ld, iw2);
+    dwX = hcf::lin2(h3, mX, hh, bX); dwV = hcf::lin2(h3, mV, hh, bV);
+    hvjp(L, ld, iw2, L.active ? ab[SC + L.l] : 0.0, ab[SC + NL + L.link], T.ddist[1], T.dd[1], dwX, dwV, bX, bV);
+    tX = tX + bX; tV = tV + bV;
+    // stage 1
+    link_cached(L.active ? db[L.l] : 0.0, db[4 * NL + L.link], ld, iw2);
+    dwX = hcf::lin2(h6, mX, hh, bX); dwV = hcf::lin2(h6, mV, hh, bV);
+    hvjp(L, ld, iw2, L.active ? ab[L.l] : 0.0, ab[NL + L.link], T.ddist[0], T.dd[0], dwX, dwV, bX, bV);
+    tX = tX + bX; tV = tV + bV;
+}
+
+__device__ __noinline__ void hvp(int N, const double *u, const double *v, const double *traj, double *dtraj,
+                                 const double *iwc, const double *adjc, const double *dic, double *Hv) {
+    (void)u; (void)traj; (void)iwc; // v, Hv may be shared memory
+    __builtin_assume(__isGlobal(dtraj)); __builtin_assume(__isGlobal(adjc)); __builtin_assume(__isGlobal(dic));
+    const Lane L;
+#if PANTR_HC_VARIANT == 3
+    constexpr int RSLOT = DSTEP + SCSTEP + DTS + 2; // reverse sweep: dic + adjc + dtraj row of one step (380 doubles)
+    __shared__ __align__(16) double ring[2 * RSLOT];
+    double (*dring)[DSTEP] = reinterpret_cast<double (*)[DSTEP]>(ring); // forward sweep: 3 dic slots in the same bytes
+    static_assert(3 * DSTEP <= 2 * RSLOT, "ring");
+#else
+    __shared__ __align__(16) double dring[3][DSTEP];
+    __shared__ __align__(16) double aring[2][SCSTEP];
+#endif
+    double dX = 0.0, dV = 0.0;
+    // ---- forward tangent sweep: dic blocks staged two steps ahead through the 3-slot ring ----
+    dt_store(L, dtraj, 0, dX, dV);
+    __syncwarp();
+    fetch160(dring[0], dic); cp_async_commit();
+    fetch160(dring[1], dic + (N > 1 ? DSTEP : 0)); cp_async_commit();
+    double vd = load_v(L, v, 0);
+    int s0 = 0, s1 = 1, s2 = 2;
+#pragma unroll 1
+    for (int k = 0; k < N; ++k) {
+        cp_async_wait_1();
+        __syncwarp();
+        const int kf = k + 2 < N ? k + 2 : N - 1;
+        fetch160(dring[s2], dic + kf * DSTEP); cp_async_commit();
+        const double vp = load_v(L, v, k + 1 < N ? k + 1 : k);
+        Tan T; double kX[4], kV[4];
+        jvp_chain(L, dring[s0], dX, dV, vd, T, kX, kV);
+        dX = hcf::rk4c(dX, kX[0], kX[1], kX[2], kX[3]);
+        dV = hcf::rk4c(dV, kV[0], kV[1], kV[2], kV[3]);
+        dt_store(L, dtraj, k + 1, dX, dV);
+        vd = vp;
+        const int t = s0; s0 = s1; s1 = s2; s2 = t;
+    }
+    cp_async_wait_all();
+    __syncwarp();
+    // ---- reverse sweep for mu = d lambda ----
+    double mX = L.isEnd ? two_alpha * dX : 0.0;
+    double mV = L.hasV ? two_beta * dV : 0.0;
+#if PANTR_HC_VARIANT == 3
+    // Everything a step needs from global memory (dic, adjc, the tangent state) arrives through one
+    // cp.async slot fetched a step ahead: no register-destination global loads inside the loop, whose
+    // scoreboard the first shared-memory read of a step otherwise ends up waiting on
+    // (15 % of all warp samples on one DMUL in the capture of variant 1).
+    {
+        double *b0 = ring;
+        fetch160(b0, dic + (N - 1) * DSTEP); fetch160(b0 + DSTEP, adjc + (N - 1) * SCSTEP);
+        fetch_row(b0 + DSTEP + SCSTEP, dtraj + (N - 1) * DTS);
+        cp_async_commit();
+    }
+    vd = load_v(L, v, N - 1);
+    int cur = 0;
+#pragma unroll 1
+    for (int k = N - 1; k >= 0; --k) {
+        cp_async_wait_all();
+        __syncwarp();
+        const double *db = ring + cur * RSLOT, *ab = db + DSTEP, *tb = ab + SCSTEP;
+        {
+            const int kn = k > 0 ? k - 1 : 0;
+            double *nb = ring + (cur ^ 1) * RSLOT;
+            fetch160(nb, dic + kn * DSTEP); fetch160(nb + DSTEP, adjc + kn * SCSTEP);
+            fetch_row(nb + DSTEP + SCSTEP, dtraj + kn * DTS);
+            cp_async_commit();
+        }
+        cur ^= 1;
+        const double vp = load_v(L, v, k > 0 ? k - 1 : 0);
+        dX = L.active ? tb[L.l] : 0.0;
+        dV = L.hasV ? tb[NL + L.l] : 0.0;
+        Tan T; double kX[4], kV[4], tX, tV;
+        jvp_chain(L, db, dX, dV, vd, T, kX, kV);
+        hvjp_chain(L, db, ab, T, mX, mV, tX, tV);
+        mX = L.isEnd ? fma(two_alpha, dX, tX) : tX;
+        if (L.hasV) mV = fma(two_beta, dV, tV);
+        else {
+            if (L.isEnd) Hv[NU * k + (L.l - NVL)] = fma(two_gamma, vd, tV);
+            mV = 0.0;
+        }
+        vd = vp;
+    }
+    cp_async_wait_all();
+#elif PANTR_HC_VARIANT == 1
+    dt_load(L, dtraj, N - 1, dX, dV);
+    vd = load_v(L, v, N - 1);
+    fetch160(dring[0], dic + (N - 1) * DSTEP); fetch160(aring[0], adjc + (N - 1) * SCSTEP);
+    cp_async_commit();
+    int cur = 0;
+#pragma unroll 1
+    for (int k = N - 1; k >= 0; --k) {
+        cp_async_wait_all();
+        __syncwarp();
+        const double *db = dring[cur], *ab = aring[cur];
+        if (k > 0) { fetch160(dring[cur ^ 1], dic + (k - 1) * DSTEP); fetch160(aring[cur ^ 1], adjc + (k - 1) * SCSTEP); }
+        cp_async_commit();
+        cur ^= 1;
+        double dXp = 0, dVp = 0, vp = 0;
+        if (k > 0) { dt_load(L, dtraj, k - 1, dXp, dVp); vp = load_v(L, v, k - 1); }
+        Tan T; double kX[4], kV[4], tX, tV;
+        jvp_chain(L, db, dX, dV, vd, T, kX, kV);
+        hvjp_chain(L, db, ab, T, mX, mV, tX, tV);
+        mX = L.isEnd ? fma(two_alpha, dX, tX) : tX;
+        if (L.hasV) mV = fma(two_beta, dV, tV);
+        else {
+            if (L.isEnd) Hv[NU * k + (L.l - NVL)] = fma(two_gamma, vd, tV);
+            mV = 0.0;
+        }
+        dX = dXp; dV = dVp; vd = vp;
+    }
+#else
+    // prologue: dic(N-1) -> slot 0 ; then adjc(N-1) and dic(N-2) -> slot 1 ; tangent chain of step N-1
+    const int k2 = N > 1 ? N - 2 : 0;
+    fetch160(dring[0], dic + (N - 1) * DSTEP); cp_async_commit();
+    fetch160(aring[0], adjc + (N - 1) * SCSTEP); fetch160(dring[1], dic + k2 * DSTEP); cp_async_commit();
+    double dXh, dVh, vdh;            // step k     (stage cost of the running step)
+    double dXj, dVj, vdj;            // step k-1   (tangent chain issued this iteration)
+    dt_load(L, dtraj, N - 1, dXh, dVh); vdh = load_v(L, v, N - 1);
+    dt_load(L, dtraj, k2, dXj, dVj);    vdj = load_v(L, v, k2);
+    cp_async_wait_1();
+    __syncwarp();
+    Tan T;
+    { double kX[4], kV[4]; jvp_chain(L, dring[0], dXh, dVh, vdh, T, kX, kV); }
+    int sh = 0, sj = 1, sf = 2, ac = 0;
+#pragma unroll 1
+    for (int k = N - 1; k >= 0; --k) {
+        cp_async_wait_all();
+        __syncwarp();
+        // fetch adjc(k-1) and dic(k-2) (indices clamped at 0: the last iteration's look-ahead work is a
+        // discarded repeat of step 0, which keeps the loop body one basic block)
+        const int ka = k > 0 ? k - 1 : 0, kd = k > 1 ? k - 2 : 0;
+        fetch160(aring[ac ^ 1], adjc + ka * SCSTEP); fetch160(dring[sf], dic + kd * DSTEP);
+        cp_async_commit();
+        double dXp, dVp;
+        dt_load(L, dtraj, kd, dXp, dVp);
+        const double vp = load_v(L, v, kd);
+        Tan Tn; double kX[4], kV[4], tX, tV;
+        jvp_chain(L, dring[sj], dXj, dVj, vdj, Tn, kX, kV);       // step k-1: independent of ...
+        hvjp_chain(L, dring[sh], aring[ac], T, mX, mV, tX, tV);   // ... step k's second-order adjoint chain
+        mX = L.isEnd ? fma(two_alpha, dXh, tX) : tX;
+        if (L.hasV) mV = fma(two_beta, dVh, tV);
+        else {
+            if (L.isEnd) Hv[NU * k + (L.l - NVL)] = fma(two_gamma, vdh, tV);
+            mV = 0.0;
+        }
+        T = Tn;
+        dXh = dXj; dVh = dVj; vdh = vdj; dXj = dXp; dVj = dVp; vdj = vp;
+        ac ^= 1;
+        const int t = sh; sh = sj; sj = sf; sf = t;
+    }
+    cp_async_wait_all();
+#endif
+    __syncwarp();
+}
+#endif
 
 } // namespace hc
 
@@ -404,14 +668,18 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
 struct HangingChain {
     static constexpr int NX = hc::NX, NU = hc::NU, NC = 0;
 #ifndef PANTR_MIN_BLOCKS
-#define PANTR_MIN_BLOCKS 16 // resident warps per SM the solve kernel is compiled for (128 registers)
+#define PANTR_MIN_BLOCKS 12 // resident warps per SM the solve kernel is compiled for (168 registers)
 #endif
     static constexpr int MIN_BLOCKS = PANTR_MIN_BLOCKS;
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int) { return 0; }
     // traj + dtraj + iwc + adjc
     __host__ __device__ static int traj_doubles(int N) {
+#if PANTR_HC_VARIANT >= 1
+        return (N + 1) * hc::DTS + ((N + 1) * NX + 1) / 2 * 2 + 4 * hc::NLINK * N + hc::SCSTEP * N + hc::DSTEP * N;
+#else
         return 2 * (N + 1) * NX + 4 * hc::NLINK * N + hc::SCSTEP * N;
+#endif
     }
     __host__ __device__ static double C_lb(int) { return -hc::v_max; } // hanging_chain.py:82-84
     __host__ __device__ static double C_ub(int) { return +hc::v_max; }
@@ -425,12 +693,17 @@ struct HangingChain {
 
     int N;
     const double *x0;
-    double *traj, *dtraj, *iwc, *adjc;
+    double *traj, *dtraj, *iwc, *adjc, *dic;
     bool hvp_ready; // adjc holds the first-order stage data of the last rollout
 
     __device__ void init(int N_, const double *x0_, double *ws) {
-        N = N_; x0 = x0_; traj = ws; dtraj = ws + (N_ + 1) * NX; iwc = ws + 2 * (N_ + 1) * NX;
-        adjc = iwc + 4 * hc::NLINK * N_; hvp_ready = false;
+        N = N_; x0 = x0_; hvp_ready = false;
+#if PANTR_HC_VARIANT >= 1
+        dtraj = ws; traj = ws + (N_ + 1) * hc::DTS; iwc = traj + ((N_ + 1) * NX + 1) / 2 * 2;
+#else
+        traj = ws; dtraj = ws + (N_ + 1) * NX; iwc = ws + 2 * (N_ + 1) * NX;
+#endif
+        adjc = iwc + 4 * hc::NLINK * N_; dic = adjc + hc::SCSTEP * N_;
     }
     __device__ double eval_f(const double *u) { return eval_psi(u, nullptr, nullptr, nullptr); }
     __device__ void eval_g(const double *, double *) {}
@@ -445,7 +718,7 @@ struct HangingChain {
         __syncwarp();
         double f = hc::rollout(N, x0, x, traj, iwc);
         __syncwarp();
-        hc::adjoint(N, x, traj, iwc, grad, adjc);
+        hc::adjoint(N, x, traj, iwc, grad, adjc, dic);
         hvp_ready = true;
         __syncwarp();
         return f;
@@ -454,7 +727,7 @@ struct HangingChain {
     __device__ void hess_psi_prod(const double *x, const double *, const double *, const double *v, double *Hv) {
         __syncwarp();
         if (!hvp_ready) (void)eval_psi_grad_psi(x, nullptr, nullptr, Hv); // Hv as scratch for the gradient
-        hc::hvp(N, x, v, traj, dtraj, iwc, adjc, Hv);
+        hc::hvp(N, x, v, traj, dtraj, iwc, adjc, dic, Hv);
         __syncwarp();
     }
     // ---- problem plugin face (m = 0: L = f) ----
