@@ -197,13 +197,13 @@ __device__ __forceinline__ void stage_fetch(const Lane &L, double *buf, const do
     if (l < 20) cp_async16(buf + SCSTEP + 2 * l, iw + 2 * l);
     (void)L;
 }
-// ---- PANTR_HC_VARIANT >= 1: the Hessian-vector product reads the stage points' link vectors from a cache ----
+// ---- PANTR_HC_DIST_CACHE: the Hessian-vector product reads the stage points' link vectors from a cache ----
 // dic  N x 160: per RK4 step the 4 x 30 lane values of `dist` at the stage points followed by the 4 x 10
 // values of 1/|dist| (a copy of the step's iwc block, so that one contiguous block feeds both sweeps of
 // the product).  Written by the adjoint sweep (depends on u only, like adjc); with it the product does
 // not rebuild the stage points (no state trajectory reads, no k_j chain, 8 shuffles fewer per stage).
-#ifndef PANTR_HC_VARIANT
-#define PANTR_HC_VARIANT 3
+#ifndef PANTR_HC_DIST_CACHE
+#define PANTR_HC_DIST_CACHE 1 // 0: the product rebuilds the stage points from traj + iwc (the r01_v9 kernel, kept for A/B runs)
 #endif
 constexpr int DSTEP = 4 * NL + 4 * NLINK; // 160 doubles
 __device__ __forceinline__ void link_cached(double dist, double iw, Link &ld, double &iw2) {
@@ -283,7 +283,7 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
         if (k > 0) { load_state(L, traj, k - 1, Xp, Vp); up = load_u(L, u, k - 1); iwp = load_iw(L, iwc, k - 1); }
         Link ld[4]; double iw2[4];
         stages_cached(L, X, V, ud, iw, ld, iw2);
-#if PANTR_HC_VARIANT >= 1
+#if PANTR_HC_DIST_CACHE
         {
             double *dc = dic + k * DSTEP;
             if (L.active) {
@@ -327,7 +327,7 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
 // Hv = hess f(u) v by forward-over-adjoint (the exact Hessian-vector product that
 // casadi_generator/__init__.py:181-189 defines as hess_psi_prod; with m = 0, psi = f).
 // traj / iwc hold the rollout of `u`; dtraj is scratch for the tangent trajectory.
-#if PANTR_HC_VARIANT == 0
+#if !PANTR_HC_DIST_CACHE
 __device__ __noinline__ void hvp(int N, const double *u, const double *v, const double *traj, double *dtraj,
                                  const double *iwc, const double *adjc, const double *, double *Hv) {
     __builtin_assume(__isGlobal(u)); __builtin_assume(__isGlobal(traj)); // v, Hv may be shared memory
@@ -436,11 +436,10 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
     }
 }
 #else
-// Variants 1 and 2: the stage points' link vectors come from dic, so neither sweep touches the state
-// trajectory.  Variant 2 software-pipelines the reverse sweep: the tangent stage chain (jvp) of step
-// k-1 depends on dtraj / dic only, so it is issued alongside the second-order adjoint chain (hvjp) of
-// step k — two independent dependency chains per warp instead of one (the kernel is bound by
-// dependent-issue latency at 4 warps per scheduler).  Same operations on the same operands as variant 0.
+// The stage points' link vectors come from dic, so neither sweep of the product touches the state
+// trajectory; same operations on the same operands as the recomputing version above, hence the same bits.
+// (Tried on top of this and dropped: software-pipelining the reverse sweep so that the tangent chain of
+// step k-1 issues alongside the second-order chain of step k; no gain, profiles/r01_v10_variants_*.log.)
 /// v_k on lanes 27..29 by an unpredicated load (the other lanes read v[3k], which nothing consumes: a
 /// predicated load followed by a zeroing move exposed the whole load latency once per step,
 /// 10 % of all warp samples in the first capture of this variant)
@@ -464,45 +463,43 @@ __device__ __forceinline__ void fetch_row(double *buf, const double *g) { // 58 
     const int l = lane_id();
     if (l < DTS / 2) cp_async16(buf + 2 * l, g + 2 * l);
 }
+// Shared-memory operands are read unpredicated: lanes 30 / 31 pick up a neighbouring entry of the slot,
+// which only their own (never consumed) results see; `active ? smem : 0` cost a predicated load, a
+// zeroing CS2R and two predicated moves per operand (16 operands per step).
 struct Tan { double ddist[4], dd[4]; };
+struct Links { Link ld[4]; double iw2[4]; };
+/// tangent stage chain of one RK4 step; db = the step's dic block (shared memory)
 __device__ __forceinline__ void jvp_chain(const Lane &L, const double *db, double dX, double dV, double vd,
-                                          Tan &T, double (&kX)[4], double (&kV)[4]) {
-    Link ld; double iw2;
-    link_cached(L.active ? db[L.l] : 0.0, db[4 * NL + L.link], ld, iw2);
-    jvp(L, ld, dX, L.hasV ? dV : vd, kX[0], kV[0], T.ddist[0], T.dd[0]);
+                                          Links &K, Tan &T, double (&kX)[4], double (&kV)[4]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) link_cached(db[j * NL + L.l], db[4 * NL + j * NLINK + L.link], K.ld[j], K.iw2[j]);
+    jvp(L, K.ld[0], dX, L.hasV ? dV : vd, kX[0], kV[0], T.ddist[0], T.dd[0]);
     double sX = hcf::axpy(hh, kX[0], dX), sV = hcf::axpy(hh, kV[0], dV);
-    link_cached(L.active ? db[NL + L.l] : 0.0, db[4 * NL + NLINK + L.link], ld, iw2);
-    jvp(L, ld, sX, L.hasV ? sV : vd, kX[1], kV[1], T.ddist[1], T.dd[1]);
+    jvp(L, K.ld[1], sX, L.hasV ? sV : vd, kX[1], kV[1], T.ddist[1], T.dd[1]);
     sX = hcf::axpy(hh, kX[1], dX); sV = hcf::axpy(hh, kV[1], dV);
-    link_cached(L.active ? db[2 * NL + L.l] : 0.0, db[4 * NL + 2 * NLINK + L.link], ld, iw2);
-    jvp(L, ld, sX, L.hasV ? sV : vd, kX[2], kV[2], T.ddist[2], T.dd[2]);
+    jvp(L, K.ld[2], sX, L.hasV ? sV : vd, kX[2], kV[2], T.ddist[2], T.dd[2]);
     sX = hcf::axpy(h, kX[2], dX); sV = hcf::axpy(h, kV[2], dV);
-    link_cached(L.active ? db[3 * NL + L.l] : 0.0, db[4 * NL + 3 * NLINK + L.link], ld, iw2);
-    jvp(L, ld, sX, L.hasV ? sV : vd, kX[3], kV[3], T.ddist[3], T.dd[3]);
+    jvp(L, K.ld[3], sX, L.hasV ? sV : vd, kX[3], kV[3], T.ddist[3], T.dd[3]);
 }
-/// second-order adjoint chain of one RK4 step; db = the step's dic block, ab = its adjc block (shared memory)
-__device__ __forceinline__ void hvjp_chain(const Lane &L, const double *db, const double *ab, const Tan &T,
+/// second-order adjoint chain of one RK4 step; ab = the step's adjc block (shared memory)
+__device__ __forceinline__ void hvjp_chain(const Lane &L, const Links &K, const double *ab, const Tan &T,
                                            double mX, double mV, double &tX, double &tV) {
-    Link ld; double iw2, dwX, dwV, bX, bV;
+    double dwX, dwV, bX, bV;
     // stage 4
-    link_cached(L.active ? db[3 * NL + L.l] : 0.0, db[4 * NL + 3 * NLINK + L.link], ld, iw2);
     dwX = h6 * mX; dwV = h6 * mV;
-    hvjp(L, ld, iw2, L.active ? ab[3 * SC + L.l] : 0.0, ab[3 * SC + NL + L.link], T.ddist[3], T.dd[3], dwX, dwV, bX, bV);
+    hvjp(L, K.ld[3], K.iw2[3], ab[3 * SC + L.l], ab[3 * SC + NL + L.link], T.ddist[3], T.dd[3], dwX, dwV, bX, bV);
     tX = mX + bX; tV = mV + bV;
     // stage 3
-    link_cached(L.active ? db[2 * NL + L.l] : 0.0, db[4 * NL + 2 * NLINK + L.link], ld, iw2);
     dwX = hcf::lin2(h3, mX, h, bX); dwV = hcf::lin2(h3, mV, h, bV);
-    hvjp(L, ld, iw2, L.active ? ab[2 * SC + L.l] : 0.0, ab[2 * SC + NL + L.link], T.ddist[2], T.dd[2], dwX, dwV, bX, bV);
+    hvjp(L, K.ld[2], K.iw2[2], ab[2 * SC + L.l], ab[2 * SC + NL + L.link], T.ddist[2], T.dd[2], dwX, dwV, bX, bV);
     tX = tX + bX; tV = tV + bV;
     // stage 2
-    link_cached(L.active ? db[NL + L.l] : 0.0, db[4 * NL + NLINK + L.link], ld, iw2);
     dwX = hcf::lin2(h3, mX, hh, bX); dwV = hcf::lin2(h3, mV, hh, bV);
-    hvjp(L, ld, iw2, L.active ? ab[SC + L.l] : 0.0, ab[SC + NL + L.link], T.ddist[1], T.dd[1], dwX, dwV, bX, bV);
+    hvjp(L, K.ld[1], K.iw2[1], ab[SC + L.l], ab[SC + NL + L.link], T.ddist[1], T.dd[1], dwX, dwV, bX, bV);
     tX = tX + bX; tV = tV + bV;
     // stage 1
-    link_cached(L.active ? db[L.l] : 0.0, db[4 * NL + L.link], ld, iw2);
     dwX = hcf::lin2(h6, mX, hh, bX); dwV = hcf::lin2(h6, mV, hh, bV);
-    hvjp(L, ld, iw2, L.active ? ab[L.l] : 0.0, ab[NL + L.link], T.ddist[0], T.dd[0], dwX, dwV, bX, bV);
+    hvjp(L, K.ld[0], K.iw2[0], ab[L.l], ab[NL + L.link], T.ddist[0], T.dd[0], dwX, dwV, bX, bV);
     tX = tX + bX; tV = tV + bV;
 }
 
@@ -511,15 +508,10 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
     (void)u; (void)traj; (void)iwc; // v, Hv may be shared memory
     __builtin_assume(__isGlobal(dtraj)); __builtin_assume(__isGlobal(adjc)); __builtin_assume(__isGlobal(dic));
     const Lane L;
-#if PANTR_HC_VARIANT == 3
     constexpr int RSLOT = DSTEP + SCSTEP + DTS + 2; // reverse sweep: dic + adjc + dtraj row of one step (380 doubles)
     __shared__ __align__(16) double ring[2 * RSLOT];
     double (*dring)[DSTEP] = reinterpret_cast<double (*)[DSTEP]>(ring); // forward sweep: 3 dic slots in the same bytes
     static_assert(3 * DSTEP <= 2 * RSLOT, "ring");
-#else
-    __shared__ __align__(16) double dring[3][DSTEP];
-    __shared__ __align__(16) double aring[2][SCSTEP];
-#endif
     double dX = 0.0, dV = 0.0;
     // ---- forward tangent sweep: dic blocks staged two steps ahead through the 3-slot ring ----
     dt_store(L, dtraj, 0, dX, dV);
@@ -535,8 +527,8 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
         const int kf = k + 2 < N ? k + 2 : N - 1;
         fetch160(dring[s2], dic + kf * DSTEP); cp_async_commit();
         const double vp = load_v(L, v, k + 1 < N ? k + 1 : k);
-        Tan T; double kX[4], kV[4];
-        jvp_chain(L, dring[s0], dX, dV, vd, T, kX, kV);
+        Tan T; Links K; double kX[4], kV[4];
+        jvp_chain(L, dring[s0], dX, dV, vd, K, T, kX, kV);
         dX = hcf::rk4c(dX, kX[0], kX[1], kX[2], kX[3]);
         dV = hcf::rk4c(dV, kV[0], kV[1], kV[2], kV[3]);
         dt_store(L, dtraj, k + 1, dX, dV);
@@ -548,11 +540,10 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
     // ---- reverse sweep for mu = d lambda ----
     double mX = L.isEnd ? two_alpha * dX : 0.0;
     double mV = L.hasV ? two_beta * dV : 0.0;
-#if PANTR_HC_VARIANT == 3
     // Everything a step needs from global memory (dic, adjc, the tangent state) arrives through one
     // cp.async slot fetched a step ahead: no register-destination global loads inside the loop, whose
     // scoreboard the first shared-memory read of a step otherwise ends up waiting on
-    // (15 % of all warp samples on one DMUL in the capture of variant 1).
+    // (15 % of all warp samples on one DMUL when the tangent state came by __ldcg: profiles/r01_v10_variant1_ncu_full_summary.csv).
     {
         double *b0 = ring;
         fetch160(b0, dic + (N - 1) * DSTEP); fetch160(b0 + DSTEP, adjc + (N - 1) * SCSTEP);
@@ -575,11 +566,11 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
         }
         cur ^= 1;
         const double vp = load_v(L, v, k > 0 ? k - 1 : 0);
-        dX = L.active ? tb[L.l] : 0.0;
-        dV = L.hasV ? tb[NL + L.l] : 0.0;
-        Tan T; double kX[4], kV[4], tX, tV;
-        jvp_chain(L, db, dX, dV, vd, T, kX, kV);
-        hvjp_chain(L, db, ab, T, mX, mV, tX, tV);
+        dX = tb[L.l];                      // lanes 30, 31 / 27..29: unused garbage (see above)
+        dV = tb[L.l < NVL ? NL + L.l : 0];
+        Tan T; Links K; double kX[4], kV[4], tX, tV;
+        jvp_chain(L, db, dX, dV, vd, K, T, kX, kV);
+        hvjp_chain(L, K, ab, T, mX, mV, tX, tV);
         mX = L.isEnd ? fma(two_alpha, dX, tX) : tX;
         if (L.hasV) mV = fma(two_beta, dV, tV);
         else {
@@ -589,75 +580,6 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
         vd = vp;
     }
     cp_async_wait_all();
-#elif PANTR_HC_VARIANT == 1
-    dt_load(L, dtraj, N - 1, dX, dV);
-    vd = load_v(L, v, N - 1);
-    fetch160(dring[0], dic + (N - 1) * DSTEP); fetch160(aring[0], adjc + (N - 1) * SCSTEP);
-    cp_async_commit();
-    int cur = 0;
-#pragma unroll 1
-    for (int k = N - 1; k >= 0; --k) {
-        cp_async_wait_all();
-        __syncwarp();
-        const double *db = dring[cur], *ab = aring[cur];
-        if (k > 0) { fetch160(dring[cur ^ 1], dic + (k - 1) * DSTEP); fetch160(aring[cur ^ 1], adjc + (k - 1) * SCSTEP); }
-        cp_async_commit();
-        cur ^= 1;
-        double dXp = 0, dVp = 0, vp = 0;
-        if (k > 0) { dt_load(L, dtraj, k - 1, dXp, dVp); vp = load_v(L, v, k - 1); }
-        Tan T; double kX[4], kV[4], tX, tV;
-        jvp_chain(L, db, dX, dV, vd, T, kX, kV);
-        hvjp_chain(L, db, ab, T, mX, mV, tX, tV);
-        mX = L.isEnd ? fma(two_alpha, dX, tX) : tX;
-        if (L.hasV) mV = fma(two_beta, dV, tV);
-        else {
-            if (L.isEnd) Hv[NU * k + (L.l - NVL)] = fma(two_gamma, vd, tV);
-            mV = 0.0;
-        }
-        dX = dXp; dV = dVp; vd = vp;
-    }
-#else
-    // prologue: dic(N-1) -> slot 0 ; then adjc(N-1) and dic(N-2) -> slot 1 ; tangent chain of step N-1
-    const int k2 = N > 1 ? N - 2 : 0;
-    fetch160(dring[0], dic + (N - 1) * DSTEP); cp_async_commit();
-    fetch160(aring[0], adjc + (N - 1) * SCSTEP); fetch160(dring[1], dic + k2 * DSTEP); cp_async_commit();
-    double dXh, dVh, vdh;            // step k     (stage cost of the running step)
-    double dXj, dVj, vdj;            // step k-1   (tangent chain issued this iteration)
-    dt_load(L, dtraj, N - 1, dXh, dVh); vdh = load_v(L, v, N - 1);
-    dt_load(L, dtraj, k2, dXj, dVj);    vdj = load_v(L, v, k2);
-    cp_async_wait_1();
-    __syncwarp();
-    Tan T;
-    { double kX[4], kV[4]; jvp_chain(L, dring[0], dXh, dVh, vdh, T, kX, kV); }
-    int sh = 0, sj = 1, sf = 2, ac = 0;
-#pragma unroll 1
-    for (int k = N - 1; k >= 0; --k) {
-        cp_async_wait_all();
-        __syncwarp();
-        // fetch adjc(k-1) and dic(k-2) (indices clamped at 0: the last iteration's look-ahead work is a
-        // discarded repeat of step 0, which keeps the loop body one basic block)
-        const int ka = k > 0 ? k - 1 : 0, kd = k > 1 ? k - 2 : 0;
-        fetch160(aring[ac ^ 1], adjc + ka * SCSTEP); fetch160(dring[sf], dic + kd * DSTEP);
-        cp_async_commit();
-        double dXp, dVp;
-        dt_load(L, dtraj, kd, dXp, dVp);
-        const double vp = load_v(L, v, kd);
-        Tan Tn; double kX[4], kV[4], tX, tV;
-        jvp_chain(L, dring[sj], dXj, dVj, vdj, Tn, kX, kV);       // step k-1: independent of ...
-        hvjp_chain(L, dring[sh], aring[ac], T, mX, mV, tX, tV);   // ... step k's second-order adjoint chain
-        mX = L.isEnd ? fma(two_alpha, dXh, tX) : tX;
-        if (L.hasV) mV = fma(two_beta, dVh, tV);
-        else {
-            if (L.isEnd) Hv[NU * k + (L.l - NVL)] = fma(two_gamma, vdh, tV);
-            mV = 0.0;
-        }
-        T = Tn;
-        dXh = dXj; dVh = dVj; vdh = vdj; dXj = dXp; dVj = dVp; vdj = vp;
-        ac ^= 1;
-        const int t = sh; sh = sj; sj = sf; sf = t;
-    }
-    cp_async_wait_all();
-#endif
     __syncwarp();
 }
 #endif
@@ -675,7 +597,7 @@ struct HangingChain {
     __host__ __device__ static int m(int) { return 0; }
     // traj + dtraj + iwc + adjc
     __host__ __device__ static int traj_doubles(int N) {
-#if PANTR_HC_VARIANT >= 1
+#if PANTR_HC_DIST_CACHE
         return (N + 1) * hc::DTS + ((N + 1) * NX + 1) / 2 * 2 + 4 * hc::NLINK * N + hc::SCSTEP * N + hc::DSTEP * N;
 #else
         return 2 * (N + 1) * NX + 4 * hc::NLINK * N + hc::SCSTEP * N;
@@ -698,7 +620,7 @@ struct HangingChain {
 
     __device__ void init(int N_, const double *x0_, double *ws) {
         N = N_; x0 = x0_; hvp_ready = false;
-#if PANTR_HC_VARIANT >= 1
+#if PANTR_HC_DIST_CACHE
         dtraj = ws; traj = ws + (N_ + 1) * hc::DTS; iwc = traj + ((N_ + 1) * NX + 1) / 2 * 2;
 #else
         traj = ws; dtraj = ws + (N_ + 1) * NX; iwc = ws + 2 * (N_ + 1) * NX;
