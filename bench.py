@@ -386,7 +386,11 @@ def run_b200(args):
                        "MEASURED_PEAKS.json has no FP64 entry",
         "hbm": {"achieved_gbs": state_bytes / (kernel_ms * 1e-3) / 1e9, "peak_gbs": hbm_peak,
                 "peak_source": "measured" if os.path.exists(peaks_file) else "fallback",
-                "algorithmic_bytes_per_launch": state_bytes},
+                "algorithmic_bytes_per_launch": state_bytes,
+                # the kernel's own cache streaming (per-block sweep caches do not fit in L2): committed
+                # ncu traffic of this launch shape over the live kernel time, the second roofline
+                "cache_stream_gbs": traffic / (kernel_ms * 1e-3) / 1e9 if traffic else None,
+                "cache_stream_frac_of_peak": traffic / (kernel_ms * 1e-3) / 1e9 / hbm_peak if traffic else None},
     }
 
     # ---- CPU baseline (rank 0, N = 1 only): the oracle port on this box's host cores ----
