@@ -46,9 +46,10 @@ struct Pantr {
     Trace tr;
 
     /// sm / smem_set: the Steihaug-CG vectors (set >= 1: z, r, d, Bd; set 2: also work, work2 and the
-    /// J/K index list) live in the block's shared memory instead of the global workspace.
+    /// J/K index list; set 3: also the CG iterate qJ) live in the block's shared memory instead of the global workspace.
     __host__ __device__ static size_t smem_bytes(int n, int set) {
-        return set == 0 ? 0 : (set == 1 ? size_t(4) * n * 8 : size_t(6) * n * 8 + size_t(n + 2) / 2 * 8);
+        return set == 0 ? 0 : (set == 1 ? size_t(4) * n * 8
+                                        : size_t(6) * n * 8 + size_t(n + 2) / 2 * 8 + (set >= 3 ? size_t(n) * 8 : 0));
     }
     __device__ Pantr(Model &mdl_, const SolverParams &P_, IterScalars *it_, int n_, int m_, Vec ws,
                      double *sm = nullptr, int smem_set = 0)
@@ -69,6 +70,7 @@ struct Pantr {
             JK = reinterpret_cast<int *>(p);
             if (smem_set >= 1) { z = sm; r = sm + n; d = sm + 2 * n; Bd = sm + 3 * n; }
             if (smem_set >= 2) { work = sm + 4 * n; work2 = sm + 5 * n; JK = reinterpret_cast<int *>(sm + 6 * n); }
+            if (smem_set >= 3) qJ = sm + 6 * n + (n + 2) / 2; // the CG iterate s: written, normed and copied every CG iteration
         }
     }
     __host__ __device__ static size_t ws_doubles(int n, int m) {
