@@ -20,7 +20,7 @@ def disturbed_states(prob, B, rng, steps=5):
     return x0
 
 
-@pytest.mark.parametrize("N", [1, 7, 60])
+@pytest.mark.parametrize("N", [1, 2, 3, 7, 60])  # 1..3: the clamped look-ahead of the product's cp.async rings
 def test_hanging_chain_eval_bit_exact(pb, N):
     prob = pb.BatchedProblem("hanging_chain", N)
     rng = np.random.default_rng(1 + N)
