@@ -20,6 +20,11 @@
 //                      link), written by the adjoint sweep: they depend on u only, and PANTR takes
 //                      ~30 Hessian-vector products per gradient, so the products' reverse sweep reads
 //                      them instead of carrying the lambda recurrence (no vjp, 25 % fewer instructions).
+//   dic   N x 160      link vectors `dist` of the 4 stage points (4 x 30) + the step's iwc block (4 x 10),
+//                      written by the adjoint sweep: the Hessian-vector product reads its stage points from
+//                      here (PANTR_HC_DIST_CACHE, default) and stages dic / adjc / dtraj rows through
+//                      shared memory with cp.async; dtraj rows are then padded to 58 doubles and dtraj
+//                      comes first in the workspace (16-byte alignment of every staged block).
 // The three sweeps are __noinline__ so that the solver contains exactly one copy of each: the
 // solve kernel's code then fits the SM instruction caches (the fully inlined version was 1.1 MB of
 // SASS and stalled 14 of 19 cycles per issue on instruction fetch: profiles/r01_v0_*).
