@@ -2,6 +2,7 @@
 // C entry points for ctypes (tests/, smoke(), bench.py cpu_baseline / --impl reference).
 #include "hanging_chain.hpp"
 #include "quadcopter.hpp"
+#include "quadcopter_condensed.hpp"
 #include "generic_problems.hpp"
 #include "oracle_alm.hpp"
 #include <atomic>
@@ -20,6 +21,9 @@ std::unique_ptr<Problem> make_problem(int problem_id, int N) {
         case 0: return std::make_unique<HangingChain>(N);
         case 1: return std::make_unique<SimpleQuadcopter>(N);
         case 2: return std::make_unique<RealisticQuadcopter>(N);
+        // 5, 6: the condensed formulation of the same two problems (operation-order mirror of the CUDA path)
+        case 5: return std::make_unique<SimpleQuadcopterCondensed>(N);
+        case 6: return std::make_unique<RealisticQuadcopterCondensed>(N);
         default: return nullptr;
     }
 }
@@ -28,6 +32,8 @@ void set_x0(Problem &p, int problem_id, const double *x0) {
     if (problem_id == 0) { auto &hc = static_cast<HangingChain &>(p); std::copy(x0, x0 + hc.NX, hc.x0.begin()); }
     if (problem_id == 1) { auto &q = static_cast<SimpleQuadcopter &>(p); std::copy(x0, x0 + 9, q.x0.begin()); }
     if (problem_id == 2) { auto &q = static_cast<RealisticQuadcopter &>(p); std::copy(x0, x0 + 9, q.x0.begin()); }
+    if (problem_id == 5) { auto &q = static_cast<SimpleQuadcopterCondensed &>(p); std::copy(x0, x0 + 9, q.x0.begin()); }
+    if (problem_id == 6) { auto &q = static_cast<RealisticQuadcopterCondensed &>(p); std::copy(x0, x0 + 9, q.x0.begin()); }
 }
 
 ALMSolver make_solver(const double *P) {
@@ -126,7 +132,7 @@ int oracle_problem_eval(int problem_id, int N, int fn, const double *x0, const d
         case 6: p->face_hess_L_prod(x, y, scalar, v, out_n); break;
         case 7:
             p->eval_hess_psi_prod(x, y, Sigma, scalar, v, out_n);
-            if (scalar != 1 && problem_id != 0) for (index_t i = 0; i < p->n; ++i) out_n[i] *= scalar;
+            if (scalar != 1 && (problem_id == 1 || problem_id == 2)) for (index_t i = 0; i < p->n; ++i) out_n[i] *= scalar;
             break;
         case 8: (void)p->eval_prox_grad_step(scalar, x, v, out_n, out_n2); break;
         case 9: p->eval_proj_diff_g(y, out_m); break;
@@ -151,6 +157,8 @@ int oracle_simulate_dynamics(int problem_id, const double *x, const double *u, d
     if (problem_id == 0) { HangingChain hc(1); hc.rk4(x, u, xn); return 0; }
     if (problem_id == 1) { pantr::quad::rk4<pantr::quad::SimpleGen>(x, u, xn, nullptr); return 0; }
     if (problem_id == 2) { pantr::quad::rk4<pantr::quad::RealisticGen>(x, u, xn, nullptr); return 0; }
+    if (problem_id == 5) { SimpleQuadcopterCondensed(1).plant_step(x, u, xn); return 0; }
+    if (problem_id == 6) { RealisticQuadcopterCondensed(1).plant_step(x, u, xn); return 0; }
     return -1;
 }
 

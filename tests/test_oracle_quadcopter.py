@@ -1,7 +1,8 @@
-"""Checks the oracle's two quadcopter models (oracle/quadcopter.hpp on csrc/quadcopter_sweeps.h and the
-sympy-generated f_c / c derivatives) against an independent numpy transcription of the reference's
-Python models and against finite differences, and the augmented-Lagrangian compositions against
-their definition.
+"""Checks the oracle's two quadcopter models, in both formulations -- problem ids 1 / 2: forward-over-adjoint
+sweeps (oracle/quadcopter.hpp), ids 5 / 6: the condensed formulation the CUDA library uses
+(oracle/quadcopter_condensed.hpp) -- against an independent numpy transcription of the reference's
+Python models and against finite differences, the augmented-Lagrangian compositions against their
+definition, and the two formulations against each other.
 
   python/alpaqa_mpc_benchmarks/problems/quadcopter.py:5-121
   python/alpaqa_mpc_benchmarks/problems/realistic_quadcopter.py:5-127
@@ -43,7 +44,8 @@ def f_c_realistic(x, u):  # realistic_quadcopter.py:30-52
     return np.concatenate([v, a, np.linalg.solve(Om, om)])
 
 
-F_C = {1: f_c_simple, 2: f_c_realistic}
+F_C = {1: f_c_simple, 2: f_c_realistic, 5: f_c_simple, 6: f_c_realistic}
+PIDS = [1, 2, 5, 6]
 
 
 def f_d(pid, x, u):  # quadcopter.py:49-55
@@ -116,13 +118,13 @@ def test_sincos_restatement():
     assert np.isnan(sb).all() and np.isnan(cb).all()
 
 
-@pytest.mark.parametrize("pid", [1, 2])
+@pytest.mark.parametrize("pid", PIDS)
 def test_dims_boxes(pid):
     assert ou.dims(pid, 60) == (240, 244, 9, 4)
     assert ou.dims(pid, 10) == (40, 44, 9, 4)
 
 
-@pytest.mark.parametrize("pid", [1, 2])
+@pytest.mark.parametrize("pid", PIDS)
 def test_plant_step_matches_independent_model(pid):
     rng = np.random.default_rng(pid)
     for _ in range(5):
@@ -130,7 +132,7 @@ def test_plant_step_matches_independent_model(pid):
         np.testing.assert_allclose(ou.simulate(pid, x0, u[:4]), f_d(pid, x0, u[:4]), rtol=1e-13, atol=1e-14)
 
 
-@pytest.mark.parametrize("pid", [1, 2])
+@pytest.mark.parametrize("pid", PIDS)
 @pytest.mark.parametrize("N", [1, 5, 20])
 def test_f_g_psi_match_independent_model(pid, N):
     rng = np.random.default_rng(100 * pid + N)
@@ -148,7 +150,7 @@ def test_f_g_psi_match_independent_model(pid, N):
     assert (yhat_r != 0).any() and (yhat_r == 0).any()  # both clamp branches are exercised
 
 
-@pytest.mark.parametrize("pid", [1, 2])
+@pytest.mark.parametrize("pid", PIDS)
 @pytest.mark.parametrize("N", [1, 4, 12])
 def test_gradient_and_hvp_finite_differences(pid, N):
     rng = np.random.default_rng(10 * pid + N)
@@ -164,7 +166,7 @@ def test_gradient_and_hvp_finite_differences(pid, N):
     np.testing.assert_allclose(Hv, (gp - gm) / (2 * h), rtol=5e-6, atol=1e-5 * np.abs(Hv).max())
 
 
-@pytest.mark.parametrize("pid", [1, 2])
+@pytest.mark.parametrize("pid", PIDS)
 def test_hvp_is_symmetric_and_linear(pid):
     N = 10
     rng = np.random.default_rng(3 + pid)
@@ -173,3 +175,51 @@ def test_hvp_is_symmetric_and_linear(pid):
     Ha, Hb, Hab = (ou.eval_(pid, N, x0, u, y=y, Sigma=S, v=w)[3] for w in (a, b, 2 * a - 3 * b))
     assert abs(a @ Hb - b @ Ha) <= 1e-10 * max(1.0, abs(a @ Hb))
     np.testing.assert_allclose(Hab, 2 * Ha - 3 * Hb, rtol=1e-9, atol=1e-9 * np.abs(Hab).max())
+
+
+@pytest.mark.parametrize("pid", [1, 2])
+@pytest.mark.parametrize("N", [1, 5, 60])
+def test_condensed_formulation_agrees_with_forward_over_adjoint(pid, N):
+    """Same exact derivatives, different association of the sums: agreement to rounding."""
+    rng = np.random.default_rng(40 * pid + N)
+    x0, u, y, S = random_point(rng, N)
+    v = rng.standard_normal(4 * N)
+    pa, ga, ya, Ha = ou.eval_(pid, N, x0, u, y=y, Sigma=S, v=v, want_yhat=True)
+    pc, gc, yc, Hc = ou.eval_(pid + 4, N, x0, u, y=y, Sigma=S, v=v, want_yhat=True)
+    assert abs(pa - pc) <= 1e-14 * abs(pa)
+    np.testing.assert_array_equal(ya, yc)
+    np.testing.assert_allclose(gc, ga, rtol=0, atol=2e-14 * np.abs(ga).max())
+    np.testing.assert_allclose(Hc, Ha, rtol=0, atol=2e-14 * np.abs(Ha).max())
+    np.testing.assert_array_equal(ou.simulate(pid + 4, x0, u[:4]), ou.simulate(pid, x0, u[:4]))
+
+
+@pytest.mark.parametrize("pid", [5, 6])
+def test_scaled_hessian_products(pid):
+    """hess_L_prod / hess_psi_prod take a scale s that multiplies the COST only: s L = s f + y' g,
+    s psi = s f + 1/2 y_hat' d (alpaqa/python/alpaqa/casadi_generator/__init__.py:65,69,146-189)."""
+    N, s = 6, -2.5
+    rng = np.random.default_rng(pid)
+    x0, u, y, S = random_point(rng, N)
+    v = rng.standard_normal(4 * N) * np.tile([1.0, 0.05, 0.05, 0.05], N)
+    h = 1e-6
+
+    def sL(uu):
+        f, g = f_g(pid, x0, uu, N)
+        return s * f + y @ g
+
+    def spsi(uu):
+        f, g = f_g(pid, x0, uu, N)
+        zl, zu = boxes(N)
+        zeta = g + y / S
+        d = zeta - np.maximum(zl, np.minimum(zeta, zu))
+        return s * f + 0.5 * (S * d) @ d
+
+    def grad_fd(fun, uu):
+        return np.array([(fun(uu + h * e) - fun(uu - h * e)) / (2 * h) for e in np.eye(4 * N)])
+
+    for fn, fun, kw in (("hess_L_prod", sL, {}), ("hess_psi_prod", spsi, {"Sigma": S})):
+        Hv = ou.problem_eval(pid, N, fn, x0, u, y=y, v=v, scalar=s, **kw)["n"]
+        fd = (grad_fd(fun, u + 1e-4 * v) - grad_fd(fun, u - 1e-4 * v)) / 2e-4
+        np.testing.assert_allclose(Hv, fd, rtol=2e-4, atol=2e-4 * np.abs(fd).max())
+        H1 = ou.problem_eval(pid, N, fn, x0, u, y=y, v=v, scalar=1.0, **kw)["n"]
+        assert np.abs(H1 - Hv).max() > 1e-3 * np.abs(H1).max()  # the scale matters

@@ -12,7 +12,13 @@ For f_c: R^9 x R^4 -> R^9 and c: R^9 -> R^4 it emits, as `PANTR_HD inline` funct
   <f>(z) ; <f>_jvp(z, dz) = J dz ; <f>_vjp(z, w) = J^T w ; <f>_hvjp(z, w, dz) = d/dz[J^T w] dz
 with the sines/cosines of the three angles passed in as `sc[6]` (they are computed once per stage
 point by pantr_sincos and cached by the rollout).  The same header is compiled into the CUDA
-library and into the CPU oracle, so both evaluate identical operation sequences.
+library and into the CPU oracle, so both evaluate identical operation sequences.  Sums of products
+are emitted as explicit fma() chains (the compilers' own contraction is off on both sides), which
+halves the FP64 instruction count of the derivative code.  Besides the functions the header
+carries FC_CONST_COLS (the columns of d f_c / d(x, u) that are constant AND only feed constant
+columns: their columns of the RK4 step Jacobian are the same for every step and every instance)
+and generated/flop_counts.json lists the exact operation count of every emitted function
+(add = mul = div = 1, fma = 2), the numerator of the roofline.
 
 Usage: python tools/gen_models.py   (writes pantr_cdc2023_experiments_b200/csrc/generated/*.h)
 """
@@ -75,27 +81,85 @@ def constraints():
 
 
 class Printer(C99CodePrinter):
+    """C printer that writes a sum with product terms as a chain of fma() and counts the operations it emits."""
+    flops = 0
+
     def _print_Pow(self, e):
         if e.exp.is_Integer and 1 < int(e.exp) <= 4:
             b = self._print(e.base)
             if not e.base.is_Atom:
                 b = "(" + b + ")"
+            Printer.flops += int(e.exp) - 1
             return "(" + "*".join([b] * int(e.exp)) + ")"
         if e.exp == -1:
+            Printer.flops += 1
             return "(1.0/" + self.parenthesize(e.base, 100) + ")"
         if e.exp.is_Integer and -4 <= int(e.exp) < -1:
             b = self._print(e.base)
             if not e.base.is_Atom:
                 b = "(" + b + ")"
+            Printer.flops += -int(e.exp)
             return "(1.0/(" + "*".join([b] * (-int(e.exp))) + "))"
         return super()._print_Pow(e)
+
+    def _print_Mul(self, e):
+        c, rest = e.as_coeff_Mul()
+        nf = len(sp.Mul.make_args(rest)) + (0 if c in (1, -1) else 1)
+        Printer.flops += max(nf - 1, 0)
+        return super()._print_Mul(e)
+
+    def _print_Integer(self, e):
+        return f"{int(e)}.0" if int(e) >= 0 else f"({int(e)}.0)"
+
+    def _split(self, t):
+        """product term -> (a, b) with t = a * b, both printed"""
+        c, rest = t.as_coeff_Mul()
+        fac = list(sp.Mul.make_args(rest)) if rest != 1 else []
+        if c not in (1, -1):
+            fac = [c] + fac
+            sign = ""
+        else:
+            sign = "-" if c == -1 else ""
+        a, b = fac[0], sp.Mul(*fac[1:])
+        return sign + self.parenthesize(a, 100), self._print(b)
+
+    @staticmethod
+    def _is_prod(t):
+        c, rest = t.as_coeff_Mul()
+        nf = (len(sp.Mul.make_args(rest)) if rest != 1 else 0) + (0 if c in (1, -1) else 1)
+        return nf >= 2
+
+    def _print_Add(self, e):
+        terms = list(e.as_ordered_terms())
+        prods = [t for t in terms if self._is_prod(t)]
+        plain = [t for t in terms if not self._is_prod(t)]
+        if not prods:
+            Printer.flops += len(terms) - 1
+            return super()._print_Add(e)
+        if plain:
+            acc = self._print(plain[0]) if len(plain) == 1 else super()._print_Add(sp.Add(*plain, evaluate=False))
+            Printer.flops += len(plain) - 1
+            rest = prods
+        else:
+            acc = self._print(prods[0])
+            rest = prods[1:]
+        for t in rest:
+            a, b = self._split(t)
+            acc = f"fma({a}, {b}, {acc})"
+            Printer.flops += 2
+        return acc
 
 
 PR = Printer({"precision": 17})
 
 
+FLOPS = {}  # emitted function name -> exact operation count (add = mul = div = 1, fma = 2)
+ALL_FLOPS = {}
+
+
 def emit(name, args, outs, exprs):
     """args: list of (c_name, symbols); outs: list of (c_name, n); exprs: flat list of sympy exprs."""
+    Printer.flops = 0
     exprs = [sp.sympify(e).subs(TRIG) for e in exprs]
     for e in exprs:
         assert not e.has(sp.sin) and not e.has(sp.cos) and not e.has(sp.tan), e
@@ -117,6 +181,8 @@ def emit(name, args, outs, exprs):
             lines.append(f"    {o}[{i}] = {PR.doprint(red[k])};")
             k += 1
     lines.append("}")
+    FLOPS[name] = Printer.flops
+    lines.insert(0, f"// {Printer.flops} flops")
     return "\n".join(lines)
 
 
@@ -137,7 +203,22 @@ def family(prefix, F, zvars, dzvars, zargs, dzargs, wsyms, wname, outs):
     return "\n\n".join(parts)
 
 
+def const_cols(fc):
+    """Columns c of J = d f_c / d(x, u) that are constant and whose nonzero rows are themselves constant columns:
+    a unit tangent in such a column stays a constant vector through every RK4 stage."""
+    z = list(x) + list(u)
+    J = sp.Matrix(fc).jacobian(sp.Matrix(z))
+    cst = {c for c in range(len(z)) if all(J[r, c].is_number for r in range(J.rows))}
+    while True:
+        bad = {c for c in cst if any(J[r, c] != 0 and r not in cst for r in range(J.rows))}
+        if not bad:
+            break
+        cst -= bad
+    return sum(1 << c for c in cst)
+
+
 def write_model(ns, fc, ref):
+    FLOPS.clear()
     body = family("fc", fc, list(x) + list(u), list(dx) + list(du), [("x", x), ("u", u)], [("dx", dx), ("du", du)],
                   w, "w", [("x", 9), ("u", 4)])
     body += "\n\n" + family("con", constraints(), list(x), list(dx), [("x", x)], [("dx", dx)], yh, "yh", [("x", 9)])
@@ -146,7 +227,11 @@ def write_model(ns, fc, ref):
             "// fc: continuous dynamics f_c(x, u); con: stage/terminal constraint c(x).  sc = {sin x6, cos x6,\n"
             "// sin x7, cos x7, sin x8, cos x8}.  *_jvp = J dz, *_vjp = J^T w, *_hvjp = d/dz[J^T w] dz.\n"
             "#pragma once\n#include \"../pantr_hd.h\"\n\n"
-            f"namespace pantr {{\nnamespace {ns} {{\n\n{body}\n\n}} // namespace {ns}\n}} // namespace pantr\n")
+            f"namespace pantr {{\nnamespace {ns} {{\n\n"
+            "// columns of d f_c / d(x, u) (bit c = column c of z = (x, u)) along which a unit tangent stays constant\n"
+            f"constexpr unsigned FC_CONST_COLS = {hex(const_cols(fc))};\n\n"
+            f"{body}\n\n}} // namespace {ns}\n}} // namespace pantr\n")
+    ALL_FLOPS[ns] = dict(FLOPS)
     path = os.path.join(OUT, f"{ns}.h")
     with open(path, "w") as fh:
         fh.write(text)
@@ -158,3 +243,7 @@ if __name__ == "__main__":
     write_model("quadcopter_gen", fc_quadcopter(), "python/alpaqa_mpc_benchmarks/problems/quadcopter.py:17-75")
     write_model("realistic_quadcopter_gen", fc_realistic_quadcopter(),
                 "python/alpaqa_mpc_benchmarks/problems/realistic_quadcopter.py:17-75")
+    import json
+    with open(os.path.join(OUT, "flop_counts.json"), "w") as fh:
+        json.dump(ALL_FLOPS, fh, indent=1, sort_keys=True)
+        fh.write("\n")
