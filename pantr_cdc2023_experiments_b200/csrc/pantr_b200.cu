@@ -4,6 +4,7 @@
 #include "pantr_device.cuh"
 #include "hanging_chain.cuh"
 #include "quadcopter.cuh"
+#include "quadcopter_condensed.cuh"
 #include "problem_face.cuh"
 #include <cstdio>
 #include <cstring>

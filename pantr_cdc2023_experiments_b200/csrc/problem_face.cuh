@@ -41,13 +41,19 @@ __global__ void __launch_bounds__(32) problem_kernel(const __grid_constant__ Pro
             case FN_G: mdl.eval_g(x, om); break;
             case FN_GRAD_G_PROD: mdl.eval_grad_g_prod(x, y, on); break;
             case FN_GRAD_L: f = mdl.eval_grad_L(x, y, on); break;
+            // scale multiplies the cost only: s L = s f + y' g, s psi = s f + 1/2 y_hat' d
+            // (casadi_generator/__init__.py:65,69); for m = 0 that is the whole product
             case FN_HESS_L_PROD:
-                mdl.hess_L_prod(x, y, v, on);
-                if (A.scalar != 1) for (int i = lane; i < n; i += 32) on[i] *= A.scalar;
+                if constexpr (Model::NC == 0) {
+                    mdl.hess_L_prod(x, y, v, on);
+                    if (A.scalar != 1) for (int i = lane; i < n; i += 32) on[i] *= A.scalar;
+                } else mdl.hess_L_prod(x, y, v, on, A.scalar);
                 break;
             case FN_HESS_PSI_PROD:
-                mdl.hess_psi_prod(x, y, S, v, on);
-                if (A.scalar != 1) for (int i = lane; i < n; i += 32) on[i] *= A.scalar;
+                if constexpr (Model::NC == 0) {
+                    mdl.hess_psi_prod(x, y, S, v, on);
+                    if (A.scalar != 1) for (int i = lane; i < n; i += 32) on[i] *= A.scalar;
+                } else mdl.hess_psi_prod(x, y, S, v, on, A.scalar);
                 break;
             case FN_PROX_GRAD_STEP: // box-constr-problem.hpp:59-64,107-114 ; out_n = x_hat, out_n2 = p
                 for (int i = lane; i < n; i += 32) {
