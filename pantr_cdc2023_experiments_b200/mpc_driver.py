@@ -166,7 +166,8 @@ def run(argv):
     print(f"\nsolver:  {solver.get_name()}\nproblem: {name} {horizon} (from {path!r})\n"
           f"num var: {n}\nnum con: {m}\nbatch:   {B} closed loops x {num_sim} MPC steps\n"
           f"time: {total:.3f} s wall, {B * num_sim / max(wall.sum(), 1e-12):.1f} solves/s on device, "
-          f"converged {100 * conv:.2f} %, mean PANTR iterations {iters.mean():.2f}\n")
+          f"converged {100 * conv:.2f} %, mean PANTR iterations {iters.mean():.2f}, "
+          f"mean Hessian-vector products {evals['ev_hess_psi_prod'].sum() / (B * num_sim):.1f} per solve\n")
     rname, ts = results_name(opts)
     extra = [("batch_size", B), ("batch_wall_time_per_step", wall), ("batch_converged_fraction", float(conv)),
              ("batch_mean_inner_iterations", float(iters.mean()))]
