@@ -44,7 +44,9 @@ enum {
     PANTR_B200_FPR_NORM, PANTR_B200_FPR_NORM2, PANTR_B200_IPOPT, PANTR_B200_LBFGSBPP
 };
 
-/* ALMParams, alpaqa/outer/alm.hpp:19-90 (wall-clock limits and printing have no device analogue) */
+/* ALMParams, alpaqa/outer/alm.hpp:19-90 (printing has no device analogue).  max_time: seconds of DEVICE wall
+ * clock (%globaltimer) an instance may spend in its solve before it returns PANTR_B200_MAX_TIME (alm.tpp:120-124,
+ * 196-210); inf = no limit. */
 typedef struct pantr_b200_alm_params {
     double tolerance, dual_tolerance, penalty_update_factor, penalty_update_factor_lower,
         min_penalty_update_factor, initial_penalty, initial_penalty_factor, initial_penalty_lower,
@@ -52,6 +54,7 @@ typedef struct pantr_b200_alm_params {
         rel_penalty_increase_threshold, max_multiplier, max_penalty, min_penalty;
     uint32_t max_iter, max_num_initial_retries, max_num_retries, max_total_num_retries;
     int32_t single_penalty_factor;
+    double max_time;
 } pantr_b200_alm_params;
 
 /* LipschitzEstimateParams, alpaqa/inner/internal/lipschitz.hpp:8-20 */
@@ -73,6 +76,7 @@ typedef struct pantr_b200_pantr_params {
     int32_t compute_ratio_using_new_stepsize, update_direction_on_prox_step,
         recompute_last_prox_step_after_direction_reset, disable_acceleration,
         ratio_approx_fbe_quadratic_model;
+    double max_time; /* seconds of device wall clock per inner solve (panoc-helpers.tpp:233-236); inf = no limit */
 } pantr_b200_pantr_params;
 
 /* SteihaugCGParams, alpaqa/accelerators/steihaugcg.hpp:9-15 */
@@ -213,25 +217,27 @@ int pantr_b200_simulate_dynamics_batch_device(pantr_b200_solver *s, int64_t B, c
 int pantr_b200_shift_warm_start_device(pantr_b200_solver *s, int64_t B, double *d_u, double *d_y,
                                        void *stream);
 
-/* Scheduling hint for the next solves (warp-per-instance path): d_order is a DEVICE array with a permutation
- * of 0..B-1; resident blocks take instances in that order instead of by index.  In closed-loop MPC the
- * previous step's per-instance cost (stats[b].cycles) predicts the next one, and starting the expensive
- * instances first shortens the tail of the launch.  Results do not depend on the order.  NULL = by index.
- * The array is caller-owned and must stay valid (and of length >= B) while it is set. */
-int pantr_b200_set_order_device(pantr_b200_solver *s, const int32_t *d_order);
+/* Scheduling hint for the next solves (warp-per-instance path): d_order is a DEVICE array of `length` int32 holding a
+ * permutation of 0..length-1; resident blocks take instances in that order instead of by index.  In closed-loop MPC
+ * the previous step's per-instance cost (stats[b].cycles) predicts the next one, and starting the expensive
+ * instances first shortens the tail of the launch.  Results do not depend on the order.  NULL / 0 = by index.
+ * The array is caller-owned and must stay valid while it is set.  A solve whose batch size differs from `length`
+ * fails with PANTR_B200_INVALID_ARGUMENT; entries outside 0..B-1 are skipped by the kernel (that instance is then not
+ * solved: its stats keep status Busy), so a non-permutation cannot read or write out of bounds.  The
+ * thread-per-instance path ignores the hint. */
+int pantr_b200_set_order_device(pantr_b200_solver *s, const int32_t *d_order, int64_t length);
 
-/* How instances map onto the GPU for the next solves: 0 = automatic (default), 1 = one warp per instance,
- * whole solves handed out by a queue, 2 = one thread per instance (32 per warp; quadcopter models only),
- * 3 = one warp per instance, PANTR *iterations* handed out by a queue (models without general constraints,
- * i.e. the hanging chain; per-instance state lives in HBM between iterations so that all instances advance at the
- * same rate).  Automatic picks 2 for the quadcopters when B >= 256, else 1.  Modes that do not apply to the
- * model fall back to 1.  Results are bit-identical in all mappings. */
+/* How instances map onto the GPU for the next solves: 0 = automatic (default), 1 = one warp per instance
+ * (hanging chain: lane = coordinate; quadcopters: condensed formulation, lanes = steps / matrix rows),
+ * 2 = one thread per instance, forward-over-adjoint sweeps (quadcopter models only; round-1 path kept for A/B).
+ * Automatic = 1.  A mode that does not apply to the model falls back to 1. */
 int pantr_b200_set_exec_mode(pantr_b200_solver *s, int mode);
 
 /* Optional per-iteration trace of one instance of the next solve_batch call (debug / parity):
  * rows of 11 doubles {k, psi, fbe, gamma, eps, radius, rho, q_model, nJ, cg_iters, accepted}. */
 int pantr_b200_set_trace(pantr_b200_solver *s, int64_t instance, int max_rows);
-int pantr_b200_get_trace(pantr_b200_solver *s, double *rows, int *n_rows);
+/* rows: room for `capacity_rows` rows; at most that many are copied.  n_rows: rows the solve produced. */
+int pantr_b200_get_trace(pantr_b200_solver *s, double *rows, int capacity_rows, int *n_rows);
 
 /* Number of kernels this handle has launched so far. */
 int64_t pantr_b200_kernel_launches(const pantr_b200_solver *s);

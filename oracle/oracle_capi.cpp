@@ -44,6 +44,9 @@ ALMSolver make_solver(const double *P) {
     a.rel_penalty_increase_threshold = P[6]; a.max_multiplier = P[7]; a.max_penalty = P[8];
     a.min_penalty = P[9]; a.max_iter = (unsigned)P[10]; a.initial_penalty_factor = P[11];
     a.single_penalty_factor = P[12] != 0;
+    a.max_num_initial_retries = (unsigned)P[13]; a.max_num_retries = (unsigned)P[14]; a.max_total_num_retries = (unsigned)P[15];
+    a.penalty_update_factor_lower = P[37]; a.min_penalty_update_factor = P[38]; a.initial_penalty_lower = P[39];
+    a.initial_tolerance_increase = P[41]; a.rho_increase = P[42]; a.rho_max = P[43];
     auto &p = s.inner_solver.params;
     p.max_iter = (unsigned)P[16]; p.stop_crit = (int)P[17]; p.L_min = P[18]; p.L_max = P[19];
     p.quadratic_upperbound_tolerance_factor = P[20]; p.TR_tolerance_factor = P[21];

@@ -49,6 +49,11 @@ inline real_t dot(const real_t *a, const real_t *b, index_t n) {
 }
 inline real_t sqnorm(const real_t *a, index_t n) { return dot(a, a, n); }
 inline real_t norm2(const real_t *a, index_t n) { return std::sqrt(sqnorm(a, n)); }
+inline real_t norm1(const real_t *a, index_t n) {
+    real_t p[32] = {};
+    for (index_t i = 0; i < n; ++i) p[i & 31] = p[i & 31] + std::fabs(a[i]);
+    return butterfly_sum(p);
+}
 /// max |a_i|; NaN if any entry is NaN.
 inline real_t norm_inf(const real_t *a, index_t n) {
     real_t m = 0;
@@ -113,6 +118,10 @@ struct Problem {
     virtual void face_grad_g_prod(const real_t *, const real_t *, real_t *) const {}
     virtual real_t face_grad_L(const real_t *, const real_t *, real_t *) const { return 0; }
     virtual void face_hess_L_prod(const real_t *, const real_t *, real_t, const real_t *, real_t *) const {}
+
+    // grad L where PANTR really needs it (stop criteria on grad psi(x_hat), pantr.tpp:246-249).  The MPC models keep
+    // eval_grad_L_impl empty because its other call site is numerically dead (pantr.tpp:306-314); they override this.
+    virtual void grad_L_live(const real_t *x, const real_t *y, real_t *g) const { eval_grad_L_impl(x, y, g); }
 
     // -- counted wrappers: problem/problem-with-counters.hpp:24-112 --
     real_t eval_f(const real_t *x) const { ++evaluations.f; return eval_f_impl(x); }

@@ -25,11 +25,19 @@ struct PANTRSolver {
     };
 
     // implementation/inner/panoc-helpers.tpp:62-137 (branches PANTR configs use)
+    // panoc-helpers.tpp:41-59
+    static bool stop_crit_requires_grad_psi_xhat(int crit) { return crit == ApproxKKT || crit == ApproxKKT2 || crit == Ipopt; }
     static real_t calc_error_stop_crit(const Problem &problem, int crit, const vec &pk, real_t gamma,
-                                       const vec &xk, const vec &grad_psik, vec &work_n1,
-                                       vec &work_n2) {
+                                       const vec &xk, const vec &xhatk, const vec &yhatk, const vec &grad_psik,
+                                       const vec &grad_psi_hatk, vec &work_n1, vec &work_n2) {
         const index_t n = problem.n;
         switch (crit) {
+            case ApproxKKT:
+            case ApproxKKT2: {
+                const real_t ig = 1 / gamma;
+                for (index_t i = 0; i < n; ++i) work_n2[i] = ig * pk[i] + (grad_psik[i] - grad_psi_hatk[i]);
+                return crit == ApproxKKT ? norm_inf(work_n2.data(), n) : norm2(work_n2.data(), n);
+            }
             case ProjGradNorm: return norm_inf(pk.data(), n);
             case ProjGradNorm2: return norm2(pk.data(), n);
             case ProjGradUnitNorm:
@@ -40,7 +48,21 @@ struct PANTRSolver {
                 return norm2(work_n2.data(), n);
             case FPRNorm: return norm_inf(pk.data(), n) / gamma;
             case FPRNorm2: return norm2(pk.data(), n) / gamma;
-            default: return NaN; // ApproxKKT/Ipopt/LBFGSBpp need grad_psi(xhat): not on the benchmarked path
+            case Ipopt: {
+                problem.eval_prox_grad_step(1, xhatk.data(), grad_psi_hatk.data(), work_n1.data(), work_n2.data());
+                real_t err = norm_inf(work_n2.data(), n);
+                auto nn    = 2 * (index_t(yhatk.size()) + n);
+                if (nn == 0) return err;
+                for (index_t i = 0; i < n; ++i) work_n2[i] = work_n2[i] - grad_psi_hatk[i];
+                real_t C_lagr_mult = norm1(work_n2.data(), n), D_lagr_mult = norm1(yhatk.data(), index_t(yhatk.size()));
+                const real_t s_max = 100, s_n = static_cast<real_t>(nn);
+                real_t s_d = std::fmax(s_max, (C_lagr_mult + D_lagr_mult) / s_n) / s_max;
+                return err / s_d;
+            }
+            case LBFGSBpp:
+                problem.eval_prox_grad_step(1, xk.data(), grad_psik.data(), work_n1.data(), work_n2.data());
+                return norm_inf(work_n2.data(), n) / std::fmax(real_t(1), norm2(xk.data(), n));
+            default: return NaN; // the reference throws std::out_of_range (panoc-helpers.tpp:136)
         }
     }
 
@@ -139,8 +161,13 @@ struct PANTRSolver {
         direction.initialize(problem, y.data(), S.data());
 
         while (true) {
-            real_t eps_k = calc_error_stop_crit(problem, params.stop_crit, curr->p, curr->gamma,
-                                                curr->x, curr->grad_psi, work_n, cand->p);
+            const bool need_grad = stop_crit_requires_grad_psi_xhat(params.stop_crit); // pantr.tpp:77,246-249
+            if (need_grad) {
+                ++problem.evaluations.grad_L;
+                problem.grad_L_live(curr->xhat.data(), curr->yhat.data(), grad_psi_xhat.data());
+            }
+            real_t eps_k = calc_error_stop_crit(problem, params.stop_crit, curr->p, curr->gamma, curr->x, curr->xhat,
+                                                curr->yhat, curr->grad_psi, grad_psi_xhat, work_n, cand->p);
             auto stop_status = check_all_stop_conditions(opts, k, eps_k, no_progress);
             if (stop_status != Busy) { // pantr.tpp:269-298
                 if (stop_status == Converged || stop_status == Interrupted ||
@@ -156,7 +183,7 @@ struct PANTRSolver {
                 return s;
             }
             // compute_FBS_step: pantr.tpp:303-319
-            eval_grad_psi_xhat(*curr, grad_psi_xhat); // result is dead (overwritten below), but counted
+            if (!need_grad) eval_grad_psi_xhat(*curr, grad_psi_xhat); // result is dead (overwritten below), but counted
             prox->x     = curr->xhat;
             prox->psi_x = curr->psi_xhat;
             prox->grad_psi.swap(grad_psi_xhat);
@@ -169,6 +196,14 @@ struct PANTRSolver {
             bool accelerated_iteration = k > 0 || direction.has_initial_direction();
             TraceRec tr{k, curr->psi_x, curr->fbe(), curr->gamma, eps_k, Delta, NaN, NaN, -1, 0, 0};
             if (accelerated_iteration && !params.disable_acceleration) {
+                // NewtonTRDirection::apply throws std::logic_error on these radii (newton-tr.hpp:96-99); the
+                // exception leaves the reference's solvers: reported as status Exception
+                if (!std::isfinite(Delta) || Delta < eps) {
+                    s.iterations = k; s.eps_ = eps_k; s.status = Exception;
+                    s.final_gamma = curr->gamma; s.final_psi = curr->psi_xhat;
+                    s.final_h = curr->h_xhat; s.final_fbe = curr->fbe();
+                    return s;
+                }
                 // compute_trust_region_step: pantr.tpp:371-392
                 real_t q_model = direction.apply(prox->gamma, prox->x.data(), prox->p.data(),
                                                  prox->grad_psi.data(), Delta, q.data());

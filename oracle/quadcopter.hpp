@@ -72,6 +72,7 @@ struct Quadcopter : Problem {
     void set_multipliers(const real_t *y) const {
         for (index_t i = 0; i < m; ++i) { w.yh[i] = y ? y[i] : 0.0; w.wact[i] = 0.0; }
     }
+    void grad_L_live(const real_t *x, const real_t *y, real_t *g) const override { (void)face_grad_L(x, y, g); }
     real_t face_grad_L(const real_t *x, const real_t *y, real_t *grad) const override {
         real_t f = eval_f_impl(x);
         set_multipliers(y);

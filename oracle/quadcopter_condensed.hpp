@@ -340,6 +340,7 @@ struct QuadcopterCondensed : Problem {
     void set_multipliers(const real_t *y) const {
         for (index_t i = 0; i < m; ++i) { yh[i] = y ? y[i] : 0.0; wact[i] = 0.0; }
     }
+    void grad_L_live(const real_t *x, const real_t *y, real_t *g) const override { (void)face_grad_L(x, y, g); }
     real_t face_grad_L(const real_t *x, const real_t *y, real_t *grad) const override {
         hvp_ready = false;
         rollout(x);

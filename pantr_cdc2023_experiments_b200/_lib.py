@@ -18,7 +18,7 @@ class ALMParamsC(C.Structure):
         "tolerance_update_factor", "rho_increase", "rho_max", "rel_penalty_increase_threshold",
         "max_multiplier", "max_penalty", "min_penalty")] + [(k, C.c_uint32) for k in (
         "max_iter", "max_num_initial_retries", "max_num_retries", "max_total_num_retries")] + [
-        ("single_penalty_factor", C.c_int32)]
+        ("single_penalty_factor", C.c_int32), ("max_time", C.c_double)]
 
 
 class LipschitzParamsC(C.Structure):
@@ -34,7 +34,7 @@ class PANTRParamsC(C.Structure):
         (k, C.c_int32) for k in (
         "compute_ratio_using_new_stepsize", "update_direction_on_prox_step",
         "recompute_last_prox_step_after_direction_reset", "disable_acceleration",
-        "ratio_approx_fbe_quadratic_model")]
+        "ratio_approx_fbe_quadratic_model")] + [("max_time", C.c_double)]
 
 
 class SteihaugParamsC(C.Structure):
@@ -111,12 +111,12 @@ def load():
     lib.pantr_b200_simulate_dynamics_batch_device.argtypes = [vp, i64, vp, vp, i64, vp, vp]
     lib.pantr_b200_shift_warm_start_device.argtypes = [vp, i64, vp, vp, vp]
     lib.pantr_b200_set_trace.argtypes = [vp, i64, C.c_int]
-    lib.pantr_b200_get_trace.argtypes = [vp, vp, C.POINTER(C.c_int)]
+    lib.pantr_b200_get_trace.argtypes = [vp, vp, C.c_int, C.POINTER(C.c_int)]
     lib.pantr_b200_kernel_launches.argtypes = [vp]
     lib.pantr_b200_kernel_launches.restype = i64
     lib.pantr_b200_grid_size.argtypes = [vp]
     lib.pantr_b200_set_exec_mode.argtypes = [vp, C.c_int]
-    lib.pantr_b200_set_order_device.argtypes = [vp, vp]
+    lib.pantr_b200_set_order_device.argtypes = [vp, vp, i64]
     lib.pantr_b200_measure_fp64_peak.argtypes = [C.c_int, C.c_int, dp]
     f64 = C.c_double
     lib.pantr_b200_eval_f_batch.argtypes = [vp, i64, vp, vp, vp]

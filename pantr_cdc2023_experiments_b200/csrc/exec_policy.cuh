@@ -131,6 +131,10 @@ __device__ __forceinline__ double xnorm_inf(A a, int n) {
     return E::nanmax_of(n, [&](int i) { return fabs(a[i]); });
 }
 template <class E, class A>
+__device__ __forceinline__ double xnorm1(A a, int n) {
+    return E::sum(n, [&](int i) { return fabs(a[i]); });
+}
+template <class E, class A>
 __device__ __forceinline__ bool xall_finite(A a, int n) {
     bool ok = true;
     for (int i = E::first(); i < n; i += E::STEP) ok = ok && isfinite(a[i]);

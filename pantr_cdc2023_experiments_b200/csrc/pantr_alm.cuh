@@ -48,6 +48,7 @@
     __device__ void alm_solve() {
         const auto &a = P.alm;
         st.status = PANTR_B200_BUSY;
+        t_alm_start = globaltimer_ns();
         if (Model::NC == 0) { // alm.tpp:29-52 (m == 0  <=>  the model has no general constraints)
             InnerResult ps = inner_solve(a.tolerance, true, Vec{}, false);
             accumulate(ps);
@@ -84,7 +85,12 @@
             InnerResult ps = inner_solve(eps_, overwrite_results, error_2, true);
             bool inner_converged = ps.status == PANTR_B200_CONVERGED;
             accumulate(ps);
-            bool backtrack = !inner_converged && !overwrite_results;
+            if (ps.status == PANTR_B200_EXCEPTION) { // an exception thrown by the direction leaves ALMSolver::operator() as well
+                st.eps = ps.eps; st.outer_iterations = i + 1; st.status = PANTR_B200_EXCEPTION;
+                return;
+            }
+            const bool out_of_time = (double)(globaltimer_ns() - t_alm_start) * 1e-9 > a.max_time; // alm.tpp:123-124
+            bool backtrack = !inner_converged && !overwrite_results && !out_of_time;
             if (backtrack) { // alm.tpp:155-187
                 if (num_successful_iters > 0) {
                     Delta = fmax(a.min_penalty_update_factor, Delta * a.penalty_update_factor_lower);
@@ -103,10 +109,10 @@
                 norm_e_2 = norm_e_1;
                 norm_e_1 = xnorm_inf<E>(error_1, m);
                 bool alm_converged = ps.eps <= a.tolerance && inner_converged && norm_e_1 <= a.dual_tolerance;
-                if (alm_converged || out_of_iter) {
+                if (alm_converged || out_of_iter || out_of_time) { // alm.tpp:200-212
                     st.eps = ps.eps; st.delta = norm_e_1; st.norm_penalty = xnorm2<E>(S, m);
                     st.outer_iterations = i + 1;
-                    st.status = alm_converged ? PANTR_B200_CONVERGED : PANTR_B200_MAX_ITER;
+                    st.status = alm_converged ? PANTR_B200_CONVERGED : out_of_time ? PANTR_B200_MAX_TIME : PANTR_B200_MAX_ITER;
                     return;
                 }
                 { Vec t = S_old; S_old = S; S = t; }

@@ -24,12 +24,6 @@ int fail(int code, const std::string &msg) { g_last_error = msg; return code; }
             return fail(PANTR_B200_CUDA_ERROR, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-
 struct KernelArgs {
     int N, n, m, nx;
     long long B;
@@ -56,7 +50,11 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
         if (lane_id() == 0) b = atomicAdd(A.counter, 1ULL);
         b = __shfl_sync(FULL, b, 0);
         if (b >= (unsigned long long)A.B) break;
-        if (A.order) b = (unsigned long long)A.order[b];
+        if (A.order) { // a hint entry outside 0..B-1 is skipped, never dereferenced as an instance
+            const int o = A.order[b];
+            if (o < 0 || (long long)o >= A.B) continue;
+            b = (unsigned long long)o;
+        }
         long long t0 = clock64();
         const unsigned long long g0 = globaltimer_ns();
         Model mdl;
@@ -80,161 +78,8 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
 
 // ---- thread-per-instance variant (ThreadExec, exec_policy.cuh): 32 instances per warp, vectors
 // interleaved across the warp.  For the small-state models whose sweeps are sequential chains. ----
-// ---- iteration-sliced variant of the solve kernel (models without general constraints: m = 0) ----
-// The launch of solve_kernel lasts as long as its slowest instances: the queue hands out whole solves
-// whose cost varies 1..4x the mean, and 21 % of the slot-time is idle at the tail (bench: slot_utilisation).
-// Here the unit of work is ONE PANTR iteration: the iterate slots (x, x_hat, grad psi, p: 12 n doubles) and the
-// loop scalars of every INSTANCE live in global memory, a resident warp pops an instance from a multi-producer /
-// multi-consumer ring, advances it by `chunk` iterations and pushes it back, so all instances progress
-// at the same rate; instances predicted to have much work left go through a second ring that is served first.
-// Same arithmetic, same results.  MEASURED (16384 warm instances): whole solves 396 ms, round-robin 393-408 ms,
-// with the priority ring 419-434 ms -- no gain: when an SM's slots run dry its remaining warps speed up, so the
-// idle slot-time of the whole-solve kernel is not really lost.  Kept behind exec mode 3.
-struct InstState {
-    int started, pad;
-    IterScalars it[3];
-    pantr_b200_stats st;
-    double s_Delta, s_rho, s_tolerance;
-    int s_curr, s_prox, s_cand, s_always, s_errz;
-    unsigned s_k, s_no_progress, pad2;
-};
-struct SliceRing {
-    unsigned long long *head, *tail, *flag; // flag[slot] = ticket + 1 while the slot holds an item, else 0
-    int *ring;
-    unsigned cap;
-};
-struct SliceQueue {
-    SliceRing urgent, normal; // instances predicted to have much work left are served first
-    unsigned long long *done;
-};
-__device__ __forceinline__ unsigned long long ld_acquire(const unsigned long long *p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.gpu.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release(unsigned long long *p, unsigned long long v) {
-    asm volatile("st.release.gpu.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-/// non-blocking: claims a ticket only if a push has already reserved it (its item is published at once)
-__device__ long long ring_try_pop(const SliceRing &R) {
-    unsigned long long h;
-    for (;;) {
-        h = ld_acquire(R.head);
-        if (h >= ld_acquire(R.tail)) return -1;
-        if (atomicCAS(R.head, h, h + 1) == h) break;
-    }
-    const unsigned slot = (unsigned)(h % R.cap);
-    while (ld_acquire(R.flag + slot) != h + 1) __nanosleep(64);
-    const int id = R.ring[slot];
-    st_release(R.flag + slot, 0ULL);
-    return id;
-}
-__device__ void ring_push(const SliceRing &R, int id) {
-    const unsigned long long t = atomicAdd(R.tail, 1ULL);
-    const unsigned slot = (unsigned)(t % R.cap);
-    while (ld_acquire(R.flag + slot) != 0ULL) __nanosleep(64);
-    R.ring[slot] = id;
-    st_release(R.flag + slot, t + 1);
-}
-__device__ long long queue_pop(const SliceQueue &Q, long long B) {
-    for (;;) {
-        long long id = ring_try_pop(Q.urgent);
-        if (id >= 0) return id;
-        id = ring_try_pop(Q.normal);
-        if (id >= 0) return id;
-        if (ld_acquire(Q.done) >= (unsigned long long)B) return -1; // every instance has finished: no more pushes
-        __nanosleep(256);
-    }
-}
-__global__ void queue_init_kernel(SliceQueue Q, long long B) {
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)Q.normal.cap; i += (long long)gridDim.x * blockDim.x) {
-        Q.normal.ring[i] = (int)(i < B ? i : 0);
-        Q.normal.flag[i] = i < B ? (unsigned long long)i + 1 : 0ULL;
-        Q.urgent.ring[i] = 0;
-        Q.urgent.flag[i] = 0ULL;
-        if (i == 0) {
-            *Q.normal.head = 0; *Q.normal.tail = (unsigned long long)B; *Q.urgent.head = 0; *Q.urgent.tail = 0;
-            *Q.done = 0;
-        }
-    }
-}
-
-template <class Model>
-__global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel_sliced(const __grid_constant__ SolverParams P,
-                                                                             const __grid_constant__ KernelArgs A,
-                                                                             const SliceQueue Q, double *inst_vec,
-                                                                             InstState *inst_state, int chunk, int urgent_cg) {
-    static_assert(Model::NC == 0, "the sliced kernel covers the m = 0 branch of ALMSolver (alm.tpp:29-52)");
-    __shared__ IterScalars it[3];
-    extern __shared__ __align__(16) double dyn_smem[];
-    using Solver = Pantr<Model>;
-    double *ws = A.ws + size_t(blockIdx.x) * A.ws_stride;
-    const int lane = lane_id();
-    for (;;) {
-        long long b = 0;
-        if (lane == 0) b = queue_pop(Q, A.B);
-        b = __shfl_sync(FULL, b, 0);
-        if (b < 0) break;
-        __threadfence(); // acquire side for every lane: the instance's state was written by another SM
-        long long t0 = clock64();
-        const unsigned long long g0 = globaltimer_ns();
-        InstState &IS = inst_state[b];
-        Model mdl;
-        mdl.init(A.N, A.x0 + b * A.nx, ws);
-        Solver S(mdl, P, it, A.n, A.m, ws + Model::traj_doubles(A.N), dyn_smem, A.smem_set);
-        double *iv = inst_vec + size_t(b) * 12 * A.n;
-        S.X = iv; S.XH = iv + 3 * A.n; S.G = iv + 6 * A.n; S.PP = iv + 9 * A.n;
-        S.x = A.u + b * A.n;
-        S.tracing = A.trace.rows != nullptr && b == A.trace.instance;
-        S.tr = A.trace;
-        typename Solver::InnerState s;
-        typename Solver::InnerResult res{PANTR_B200_BUSY, INFINITY, 0};
-        bool done;
-        if (!IS.started) {
-            memset(&S.st, 0, sizeof(S.st));
-            __syncwarp();
-            done = !S.inner_begin(s, res, P.alm.tolerance, true, false);
-        } else {
-            S.st = IS.st;
-            s.curr = IS.s_curr; s.prox = IS.s_prox; s.cand = IS.s_cand; s.k = IS.s_k; s.no_progress = IS.s_no_progress;
-            s.Delta = IS.s_Delta; s.rho = IS.s_rho; s.tolerance = IS.s_tolerance;
-            s.always_overwrite = IS.s_always; s.has_errz = IS.s_errz;
-            if (lane == 0) { it[0] = IS.it[0]; it[1] = IS.it[1]; it[2] = IS.it[2]; }
-            __syncwarp();
-            done = false;
-        }
-        for (int c = 0; c < chunk && !done; ++c) done = S.inner_iterate(s, res, nullptr);
-        __syncwarp();
-        S.st.cycles += (unsigned long long)(clock64() - t0);
-        S.st.elapsed_us += (unsigned)((globaltimer_ns() - g0) / 1000);
-        if (done) { // alm.tpp:29-52
-            S.accumulate(res);
-            S.st.eps = res.eps; S.st.delta = 0; S.st.norm_penalty = 0; S.st.outer_iterations = 1;
-            S.st.status = res.status;
-            if (lane == 0) A.stats[b] = S.st;
-            __threadfence();
-            __syncwarp();
-            if (lane == 0) atomicAdd(Q.done, 1ULL);
-        } else {
-            if (lane == 0) {
-                IS.st = S.st;
-                IS.s_curr = s.curr; IS.s_prox = s.prox; IS.s_cand = s.cand; IS.s_k = s.k; IS.s_no_progress = s.no_progress;
-                IS.s_Delta = s.Delta; IS.s_rho = s.rho; IS.s_tolerance = s.tolerance;
-                IS.s_always = s.always_overwrite; IS.s_errz = s.has_errz;
-                IS.it[0] = it[0]; IS.it[1] = it[1]; IS.it[2] = it[2];
-                IS.started = 1;
-            }
-            __threadfence(); // release side: the iterate slots written by all lanes, the scalars by lane 0
-            __syncwarp();
-            // Remaining-work predictor (oracle study): a short CG run in the second PANTR iteration
-            // (<= 5 iterations) precedes 84 % of the >12-iteration solves; anything alive after 6 is long too.
-            const bool urgent = urgent_cg >= 0 && ((s.k >= 2 && S.cg_last <= (unsigned)urgent_cg) || s.k >= 6);
-            if (lane == 0) ring_push(urgent ? Q.urgent : Q.normal, (int)b);
-        }
-        __syncwarp();
-    }
-}
-
+// (Round 1 also had an iteration-sliced variant of solve_kernel -- PANTR iterations handed out through a device-side
+// MPMC ring, per-instance iterate slots in HBM: bit-identical, measured equal or slower, removed.)
 #ifndef PANTR_THREAD_MIN_BLOCKS
 #define PANTR_THREAD_MIN_BLOCKS 8 // resident warps per SM the thread-per-instance kernel is compiled for
 #endif

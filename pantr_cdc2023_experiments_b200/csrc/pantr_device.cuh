@@ -42,6 +42,7 @@ struct Pantr {
     IVec JK;
     pantr_b200_stats st;
     unsigned cg_last;
+    unsigned long long t_alm_start = 0, t_inner_start = 0; // %globaltimer at the start of the ALM / the inner solve
     bool tracing;
     Trace tr;
 

@@ -3,11 +3,23 @@
 
     struct InnerResult { int status; double eps; unsigned iterations; };
 
-    // panoc-helpers.tpp:62-137 (criteria that do not need grad psi(x_hat))
+    // panoc-helpers.tpp:41-59
+    __device__ __forceinline__ bool stop_crit_requires_grad_psi_xhat() const {
+        const int c = P.pantr.stop_crit;
+        return c == PANTR_B200_APPROX_KKT || c == PANTR_B200_APPROX_KKT2 || c == PANTR_B200_IPOPT;
+    }
+    // panoc-helpers.tpp:62-137 ; gxh = grad psi(x_hat) = grad L(x_hat, y_hat) where the criterion needs it
     __device__ __noinline__ double calc_error_stop_crit(int c) {
         const int crit = P.pantr.stop_crit;
-        const CVec pk = PP + c * n;
+        const CVec pk = PP + c * n, gk = G + c * n;
         switch (crit) {
+            case PANTR_B200_APPROX_KKT:
+            case PANTR_B200_APPROX_KKT2: {
+                const double ig = 1 / it[c].gamma;
+                for (int i = E::first(); i < n; i += E::STEP) wn2[i] = ig * pk[i] + (gk[i] - gxh[i]);
+                E::sync();
+                return crit == PANTR_B200_APPROX_KKT ? xnorm_inf<E>(wn2, n) : xnorm2<E>(wn2, n);
+            }
             case PANTR_B200_PROJ_GRAD_NORM: return xnorm_inf<E>(pk, n);
             case PANTR_B200_PROJ_GRAD_NORM2: return xnorm2<E>(pk, n);
             case PANTR_B200_PROJ_GRAD_UNIT_NORM:
@@ -20,8 +32,29 @@
                 return xnorm2<E>(wn2, n);
             case PANTR_B200_FPR_NORM: return xnorm_inf<E>(pk, n) / it[c].gamma;
             case PANTR_B200_FPR_NORM2: return xnorm2<E>(pk, n) / it[c].gamma;
-            default: return nan("");
+            case PANTR_B200_IPOPT: {
+                prox_grad_step_raw(1.0, XH + c * n, gxh, wn1, wn2);
+                E::sync();
+                const double err = xnorm_inf<E>(wn2, n);
+                const int nn = 2 * (m + n);
+                if (nn == 0) return err;
+                for (int i = E::first(); i < n; i += E::STEP) wn2[i] = wn2[i] - gxh[i];
+                E::sync();
+                const double C_lagr_mult = xnorm1<E>(wn2, n), D_lagr_mult = xnorm1<E>(YH + c * m, m);
+                const double s_max = 100, s_n = (double)nn;
+                const double s_d = fmax(s_max, (C_lagr_mult + D_lagr_mult) / s_n) / s_max;
+                return err / s_d;
+            }
+            case PANTR_B200_LBFGSBPP:
+                prox_grad_step_raw(1.0, X + c * n, G + c * n, wn1, wn2);
+                E::sync();
+                return xnorm_inf<E>(wn2, n) / fmax(1.0, xnorm2<E>(X + c * n, n));
+            default: return nan(""); // rejected by the host (std::out_of_range in the reference)
         }
+    }
+    __device__ __forceinline__ bool out_of_time() const { // panoc-helpers.tpp:233-236: min(params.max_time, opts.max_time)
+        const unsigned long long now = globaltimer_ns();
+        return (double)(now - t_inner_start) * 1e-9 > P.pantr.max_time || (double)(now - t_alm_start) * 1e-9 > P.alm.max_time;
     }
 
     // x (in/out) lives in this->x ; y in this->y ; Sigma in this->Sig ; err_z -> errz (may be null)
@@ -40,6 +73,7 @@
         const auto &pp = P.pantr;
         s.curr = 0; s.prox = 1; s.cand = 2;
         const int curr = 0, cand = 2;
+        t_inner_start = globaltimer_ns();
         res = InnerResult{PANTR_B200_BUSY, INFINITY, 0};
         s.always_overwrite = always_overwrite; s.has_errz = has_errz;
         xcopy<E>(X + curr * n, x, n); // pantr.tpp:195
@@ -96,9 +130,16 @@
         const double tolerance = s.tolerance;
         const bool always_overwrite = s.always_overwrite, has_errz = s.has_errz;
         E::sync();
+        const bool need_grad = stop_crit_requires_grad_psi_xhat();
+        if (need_grad) { // pantr.tpp:246-249: grad psi(x_hat) = grad L(x_hat, y_hat)
+            ++st.ev_grad_L;
+            (void)mdl.eval_grad_L(XH + curr * n, m > 0 ? CVec(YH + curr * m) : CVec{}, gxh);
+            E::sync();
+        }
         double eps_k = calc_error_stop_crit(curr);
-        // check_all_stop_conditions: panoc-helpers.tpp:215-249 (no wall clock / stop signal on device)
+        // check_all_stop_conditions: panoc-helpers.tpp:215-249 (device clock; no stop signal on device)
         int stop = eps_k <= tolerance                    ? PANTR_B200_CONVERGED
+                   : out_of_time()                       ? PANTR_B200_MAX_TIME
                    : k == pp.max_iter                    ? PANTR_B200_MAX_ITER
                    : !isfinite(eps_k)                    ? PANTR_B200_NOT_FINITE
                    : no_progress > pp.max_no_progress    ? PANTR_B200_NO_PROGRESS
@@ -120,9 +161,9 @@
             return true;
         }
         // ---- compute_FBS_step: pantr.tpp:303-319 ----
-        // The reference evaluates grad_L(x_hat, y_hat) here and immediately overwrites the
-        // result with psi_grad_psi(prox.x): numerically dead, so only counted.
-        ++st.ev_grad_L;
+        // Unless the stop criterion already needed it, the reference evaluates grad_L(x_hat, y_hat) here and
+        // immediately overwrites the result with psi_grad_psi(prox.x): numerically dead, so only counted.
+        if (!need_grad) ++st.ev_grad_L;
         xcopy<E>(X + prox * n, XH + curr * n, n);
         double cg_ = it[curr].gamma, cL_ = it[curr].L, cpsi = it[curr].psi_xh;
         E::sync();
@@ -137,6 +178,14 @@
         double q_model = nan(""); int nJ = -1; unsigned cgi = 0;
         const double tr_psi = it[curr].psi_x, tr_fbe = fbe(curr), tr_gamma = it[curr].gamma, tr_Delta = Delta;
         if (accelerated_iteration && !pp.disable_acceleration) {
+            // NewtonTRDirection::apply throws std::logic_error on these radii (newton-tr.hpp:96-99); the exception
+            // leaves the reference's solver, here the instance ends with status Exception
+            if (!isfinite(Delta) || Delta < 2.220446049250313e-16) {
+                res.status = PANTR_B200_EXCEPTION; res.eps = eps_k; res.iterations = k;
+                st.final_gamma = it[curr].gamma; st.final_psi = it[curr].psi_xh; st.final_h = it[curr].h; st.final_fbe = fbe(curr);
+                E::sync();
+                return true;
+            }
             // compute_trust_region_step: pantr.tpp:371-392
             q_model = direction_apply(it[prox].gamma, X + prox * n, PP + prox * n, G + prox * n, Delta, q, nJ);
             cgi = cg_last; st.cg_iterations += cg_last;

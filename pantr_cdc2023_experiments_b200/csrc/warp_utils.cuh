@@ -11,6 +11,11 @@ namespace pantr {
 constexpr unsigned FULL = 0xffffffffu;
 
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 __device__ __forceinline__ double shfl(double v, int src) {
     int lo = __double2loint(v), hi = __double2hiint(v);
     lo = __shfl_sync(FULL, lo, src);

@@ -39,7 +39,7 @@ class LipschitzEstimateParams:
 class PANTRParams:
     Lipschitz: LipschitzEstimateParams = field(default_factory=LipschitzEstimateParams)
     max_iter: int = 100
-    max_time: float = 300.0  # seconds; accepted for option compatibility, not enforced on device
+    max_time: float = 300.0  # seconds (pantr.hpp:27: 5 min); enforced on the device clock
     L_min: float = 1e-5
     L_max: float = 1e20
     stop_crit: str = "ApproxKKT"
@@ -74,7 +74,7 @@ class PANTRParams:
                   "radius_factor_acceptable", "radius_factor_good", "initial_radius", "min_radius",
                   "compute_ratio_using_new_stepsize", "update_direction_on_prox_step",
                   "recompute_last_prox_step_after_direction_reset", "disable_acceleration",
-                  "ratio_approx_fbe_quadratic_model"):
+                  "ratio_approx_fbe_quadratic_model", "max_time"):
             setattr(c, f, getattr(self, f))
         return c
 
@@ -99,7 +99,7 @@ class ALMParams:
     max_penalty: float = 1e9
     min_penalty: float = 1e-9
     max_iter: int = 100
-    max_time: float = 300.0  # seconds; accepted, not enforced on device
+    max_time: float = 300.0  # seconds (alm.hpp:66: 5 min); enforced on the device clock
     max_num_initial_retries: int = 0
     max_num_retries: int = 0
     max_total_num_retries: int = 0

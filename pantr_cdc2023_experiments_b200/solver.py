@@ -299,13 +299,15 @@ class ALMSolver:
     def set_order(self, problem, order_t):
         """Scheduling hint: int32 CUDA tensor with a permutation of range(B) (kept alive here), or None."""
         self._order = order_t
+        if order_t is not None and (str(order_t.dtype) != "torch.int32" or not order_t.is_contiguous() or not order_t.is_cuda):
+            raise ValueError("order must be a contiguous int32 CUDA tensor")
         ptr = None if order_t is None else C.c_void_p(order_t.data_ptr())
-        _lib.check(_lib.load().pantr_b200_set_order_device(self._handle(problem).h, ptr))
+        _lib.check(_lib.load().pantr_b200_set_order_device(self._handle(problem).h, ptr, 0 if order_t is None else order_t.numel()))
 
     def set_exec_mode(self, problem, mode):
-        """'auto' | 'warp' (one warp per instance, whole solves) | 'thread' (one thread per instance, quadcopters
-        only) | 'sliced' (one warp per instance, PANTR iterations handed out one by one; hanging chain only)."""
-        code = {"auto": 0, "warp": 1, "thread": 2, "sliced": 3}[mode]
+        """'auto' = 'warp' (one warp per instance; quadcopters: condensed formulation) | 'thread' (one thread per
+        instance, forward-over-adjoint sweeps: quadcopters only, the round-1 path kept for A/B runs)."""
+        code = {"auto": 0, "warp": 1, "thread": 2}[mode]
         _lib.check(_lib.load().pantr_b200_set_exec_mode(self._handle(problem).h, code))
 
     def set_trace(self, problem, instance, max_rows=4096):
@@ -313,7 +315,7 @@ class ALMSolver:
 
     def get_trace(self, problem, max_rows=4096):
         rows = np.zeros((max_rows, 11)); n = C.c_int()
-        _lib.check(_lib.load().pantr_b200_get_trace(self._handle(problem).h, _ptr(rows), C.byref(n)))
+        _lib.check(_lib.load().pantr_b200_get_trace(self._handle(problem).h, _ptr(rows), max_rows, C.byref(n)))
         return rows[:min(n.value, max_rows)]
 
     def kernel_launches(self, problem):

@@ -48,6 +48,9 @@ def pack_params(solver):
                   p.Lipschitz.L_0, p.Lipschitz.ε, p.Lipschitz.δ, p.Lipschitz.Lγ_factor,
                   p.compute_ratio_using_new_stepsize, p.recompute_last_prox_step_after_direction_reset,
                   p.disable_acceleration, p.ratio_approx_fbe_quadratic_model]
+    par[13:16] = [a.max_num_initial_retries, a.max_num_retries, a.max_total_num_retries]
+    par[37:40] = [a.penalty_update_factor_lower, a.min_penalty_update_factor, a.initial_penalty_lower]
+    par[41:44] = [a.initial_tolerance_increase, a.ρ_increase, a.ρ_max]
     par[40] = d.hessian_vec_factor
     par[44:48] = [c.tol_scale, c.tol_scale_root, c.tol_max, c.max_iter_factor]
     return par
