@@ -87,6 +87,10 @@ struct ALMSolver {
             bool inner_converged = ps.status == Converged;
             s.inner_convergence_failures += !inner_converged;
             accumulate(s, ps);
+            if (ps.status == Exception) { // std::logic_error of the direction (newton-tr.hpp:96-99) leaves operator()
+                s.eps_ = ps.eps_; s.delta = 0; s.outer_iterations = i + 1; s.status = Exception;
+                return s;
+            }
             bool backtrack = !inner_converged && !overwrite_results;
             if (backtrack) { // alm.tpp:155-187
                 if (num_successful_iters > 0) {

@@ -1,0 +1,128 @@
+"""GPU parity of the solver branches the benchmark option set never takes (VERDICT r01 'weak 2'): every case is one
+option override on top of new-benchmarks-paper/dodo.py's PANTR options, solved on the device and by the CPU oracle,
+compared bit for bit (status, iteration counts, evaluation counters, iterate, multipliers, per-iteration trace).
+
+  alm-helpers.tpp:16-59   initialize_penalty, single_penalty_factor
+  alm.tpp:155-187         backtrack branch (max_num_retries > 0 and an inner solve that hits solver.max_iter)
+  panoc-helpers.tpp:62-137 all ten stop criteria (ApproxKKT = alpaqa's default, FPRNorm = the driver's default)
+  pantr.tpp:200-217       Lipschitz.L_0 > 0
+  pantr.tpp:139,155,187,200 compute_ratio_using_new_stepsize, recompute_last_prox_step_after_direction_reset,
+                          disable_acceleration
+  newton-tr.hpp:96-99     invalid trust radius -> exception (status Exception here)
+"""
+import numpy as np
+import pytest
+
+import oracle_util as ou
+
+pytestmark = pytest.mark.gpu
+MODELS = {"hanging_chain": 0, "quadcopter": 5, "realistic_quadcopter": 6}  # oracle ids of the device formulations
+STOP_CRITS = ["ApproxKKT", "ApproxKKT2", "ProjGradNorm", "ProjGradNorm2", "ProjGradUnitNorm", "ProjGradUnitNorm2",
+              "FPRNorm", "FPRNorm2", "Ipopt", "LBFGSBpp"]
+COUNTERS = ("ev_psi", "ev_psi_grad_psi", "ev_grad_L", "ev_hess_psi_prod", "ev_prox_grad_step", "ev_grad_psi",
+            "ev_inactive_indices_res_lna", "ev_proj_multipliers")
+
+
+@pytest.fixture(scope="module")
+def pb():
+    import pantr_cdc2023_experiments_b200 as pb
+    return pb
+
+
+def instances(pb, name, N, B, seed):
+    prob = pb.BatchedProblem(name, N)
+    rng = np.random.default_rng(seed)
+    x0 = np.tile(prob.initial_state(), (B, 1))
+    if name == "hanging_chain":
+        for _ in range(5):
+            x0 = prob.simulate_dynamics(x0, rng.uniform(-1, 1, (B, 3)))
+    else:
+        x0[1:] += 0.03 * rng.standard_normal((B - 1, prob.nx))
+    return prob, x0
+
+
+def solve_both(pb, name, N, B, extra, seed=0, expect_status=None):
+    solver, used = pb.make_solver(pb.benchmark_options(name) + extra)
+    assert all(used[-len(extra):]), "option not consumed"
+    prob, x0 = instances(pb, name, N, B, seed)
+    u = np.tile(prob.initial_guess(), (B, 1)); y = np.zeros((B, prob.m))
+    solver.set_trace(prob, 0, 4096)
+    st = solver(prob, u, y if prob.m else None, x0=x0)
+    trace = solver.get_trace(prob, 4096)
+    par = ou.pack_params(solver)
+    pid = MODELS[name]
+    for b in range(B):
+        uo, yo, so, tro = ou.solve(pid, N, par, x0[b], prob.initial_guess(), trace_rows=4096 if b == 0 else 0)
+        assert int(so["status"]) == st["status"][b], (extra, b, so["status"], st["status"][b])
+        assert int(so["outer_iterations"]) == st["outer_iterations"][b]
+        assert int(so["inner_iterations"]) == st["inner_iterations"][b]
+        for k in COUNTERS:
+            assert int(so[k]) == int(st[k][b]), (extra, k)
+        np.testing.assert_array_equal(u[b], uo)
+        if prob.m:
+            np.testing.assert_array_equal(y[b], yo)
+            assert so["delta"] == st["delta"][b] and so["norm_penalty"] == st["norm_penalty"][b]
+        assert so["eps"] == st["eps"][b] or (np.isnan(so["eps"]) and np.isnan(st["eps"][b]))
+        if b == 0:
+            np.testing.assert_array_equal(trace, tro)
+    if expect_status is not None:
+        assert (st["status"] == expect_status).all(), st["status"]
+    return st
+
+
+@pytest.mark.parametrize("name", ["quadcopter", "realistic_quadcopter"])
+@pytest.mark.parametrize("extra", [
+    ["alm.initial_penalty=0"],                                   # initialize_penalty from f(x0), g(x0)
+    ["alm.initial_penalty=0", "alm.initial_penalty_factor=1e3"],
+    ["alm.single_penalty_factor=1"],
+    ["alm.single_penalty_factor=1", "alm.initial_penalty=0"],
+    ["alm.max_num_retries=2", "alm.max_num_initial_retries=2", "alm.max_total_num_retries=3", "solver.max_iter=15"],
+    ["alm.max_num_retries=3", "alm.max_total_num_retries=3", "solver.max_iter=40", "alm.penalty_update_factor_lower=0.5"],
+], ids=lambda e: " ".join(e))
+def test_alm_branches(pb, name, extra):
+    solve_both(pb, name, 8, 3, extra, seed=1)
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("crit", STOP_CRITS)
+def test_stop_criteria(pb, name, crit):
+    st = solve_both(pb, name, 8, 3, [f"solver.stop_crit={crit}"], seed=2)
+    assert (st["status"] == 1).all()
+    if crit in ("ApproxKKT", "ApproxKKT2", "Ipopt"):  # grad psi(x_hat) once per loop pass, the final one included
+        assert (st["ev_grad_L"] == st["inner_iterations"] + st["outer_iterations"]).all()
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+@pytest.mark.parametrize("extra", [
+    ["solver.Lipschitz.L_0=1"],
+    ["solver.Lipschitz.L_0=1e3"],
+    ["solver.compute_ratio_using_new_stepsize=1"],
+    ["solver.recompute_last_prox_step_after_direction_reset=1"],
+    ["solver.compute_ratio_using_new_stepsize=1", "solver.recompute_last_prox_step_after_direction_reset=1"],
+    ["solver.disable_acceleration=1", "solver.max_iter=60", "alm.max_iter=5"],
+    ["solver.ratio_approx_fbe_quadratic_model=0"],
+    ["dir.hessian_vec_factor=0"],
+    ["dir.hessian_vec_factor=0.5", "accel.max_iter_factor=0.1"],
+], ids=lambda e: " ".join(e))
+def test_pantr_branches(pb, name, extra):
+    solve_both(pb, name, 8, 3, extra, seed=3)
+
+
+@pytest.mark.parametrize("name", list(MODELS))
+def test_invalid_trust_radius_is_an_exception(pb, name):
+    """newton-tr.hpp:96-99 throws std::logic_error("Trust radius too small"); the instance reports Exception (7)."""
+    st = solve_both(pb, name, 6, 2, ["solver.min_radius=0", "solver.initial_radius=1e-300"], seed=4, expect_status=7)
+    assert (st["inner_iterations"] == 0).all()
+
+
+@pytest.mark.parametrize("name", ["hanging_chain", "quadcopter"])
+def test_max_time_on_the_device_clock(pb, name):
+    """alm.max_time / solver.max_time are enforced with %globaltimer: a 1 ns budget ends every instance with MaxTime (2)
+    at its first stop test (panoc-helpers.tpp:233-243: Converged > MaxTime > MaxIter)."""
+    for extra in (["alm.max_time=1ns"], ["solver.max_time=1ns"]):
+        solver, _ = pb.make_solver(pb.benchmark_options(name) + extra)
+        prob, x0 = instances(pb, name, 6, 4, 5)
+        u = np.tile(prob.initial_guess(), (4, 1)); y = np.zeros((4, prob.m))
+        st = solver(prob, u, y if prob.m else None, x0=x0)
+        assert (st["status"] == 2).all(), (extra, st["status"])
+        assert (st["inner_iterations"] == 0).all()
