@@ -76,11 +76,25 @@ def solve_both(pb, name, N, B, extra, seed=0, expect_status=None):
     ["alm.initial_penalty=0", "alm.initial_penalty_factor=1e3"],
     ["alm.single_penalty_factor=1"],
     ["alm.single_penalty_factor=1", "alm.initial_penalty=0"],
-    ["alm.max_num_retries=2", "alm.max_num_initial_retries=2", "alm.max_total_num_retries=3", "solver.max_iter=15"],
-    ["alm.max_num_retries=3", "alm.max_total_num_retries=3", "solver.max_iter=40", "alm.penalty_update_factor_lower=0.5"],
 ], ids=lambda e: " ".join(e))
-def test_alm_branches(pb, name, extra):
+def test_alm_penalty_initialisation(pb, name, extra):
     solve_both(pb, name, 8, 3, extra, seed=1)
+
+
+@pytest.mark.parametrize("name", ["quadcopter", "realistic_quadcopter"])
+@pytest.mark.parametrize("N", [8, 12])
+@pytest.mark.parametrize("extra", [
+    ["alm.max_num_retries=2", "alm.max_num_initial_retries=2", "alm.max_total_num_retries=3", "solver.max_iter=2"],
+    ["alm.max_num_retries=2", "alm.max_num_initial_retries=2", "alm.max_total_num_retries=4", "solver.max_iter=3",
+     "alm.initial_tolerance=1e-3"],
+    ["alm.max_num_retries=3", "alm.max_total_num_retries=3", "solver.max_iter=4", "alm.penalty_update_factor_lower=0.5",
+     "alm.initial_tolerance=1e-2"],
+], ids=lambda e: " ".join(e))
+def test_alm_backtrack_branch(pb, name, N, extra):
+    """alm.tpp:155-187: an inner solve that runs out of iterations while penalty-factor updates are still allowed
+    lowers the penalty (initial_penalty_lower / penalty_update_factor_lower) and retries."""
+    st = solve_both(pb, name, N, 3, extra, seed=1)
+    assert (st["inner_convergence_failures"] > 0).any()  # the branch was taken
 
 
 @pytest.mark.parametrize("name", list(MODELS))
