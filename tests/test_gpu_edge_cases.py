@@ -27,7 +27,8 @@ def test_empty_batch_is_a_no_op(pb):
 
 @pytest.mark.parametrize("mode", ["warp", "thread"])
 def test_non_finite_initial_state_is_handled_like_the_oracle(pb, mode):
-    name, pid, N, B = "quadcopter", 1, 6, 34
+    name, N, B = "quadcopter", 6, 34
+    pid = {"warp": 5, "thread": 1}[mode]  # oracle formulation of each device path
     solver, _ = pb.make_solver(pb.benchmark_options(name))
     prob = pb.BatchedProblem(name, N)
     solver.set_exec_mode(prob, mode)
@@ -66,7 +67,7 @@ def test_iteration_caps_report_max_iter_like_the_oracle(pb):
 
 def test_largest_horizon_of_the_realistic_quadcopter_sweep(pb):
     """BASELINE configs[3]: N = 10..120; n = 480, m = 484 at the top end."""
-    name, pid, N, B = "realistic_quadcopter", 2, 120, 3
+    name, pid, N, B = "realistic_quadcopter", 6, 120, 3
     prob = pb.BatchedProblem(name, N)
     assert (prob.n, prob.m) == (480, 484)
     rng = np.random.default_rng(12)
@@ -78,20 +79,35 @@ def test_largest_horizon_of_the_realistic_quadcopter_sweep(pb):
         po, go, yo, Ho = ou.eval_(pid, N, x0[b], u[b], y=y[b], Sigma=S[b], v=v[b], want_yhat=True)
         assert po == psi[b]
         np.testing.assert_array_equal(go, grad[b]); np.testing.assert_array_equal(Ho, Hv[b])
-    # a capped solve in both mappings (a full solve at N = 120 takes ~10^4 iterations)
+    # a capped solve in both mappings, each against its own oracle formulation
     solver, _ = pb.make_solver(pb.benchmark_options(name) + ["alm.max_iter=2", "solver.max_iter=15"])
     par = ou.pack_params(solver)
-    res = {}
-    for mode in ("warp", "thread"):
+    for mode, opid in (("warp", 6), ("thread", 2)):
         solver.set_exec_mode(prob, mode)
         uu = np.tile(prob.initial_guess(), (B, 1)); yy = np.zeros((B, prob.m))
-        res[mode] = (uu, yy, solver(prob, uu, yy, x0=x0))
+        st = solver(prob, uu, yy, x0=x0)
+        uo, yo, so, _ = ou.solve(opid, N, par, x0[1], prob.initial_guess())
+        np.testing.assert_array_equal(uu[1], uo); np.testing.assert_array_equal(yy[1], yo)
+        assert int(so["status"]) == st["status"][1] and int(so["inner_iterations"]) == st["inner_iterations"][1]
     solver.set_exec_mode(prob, "auto")
-    np.testing.assert_array_equal(res["warp"][0], res["thread"][0])
-    np.testing.assert_array_equal(res["warp"][1], res["thread"][1])
-    uo, yo, so, _ = ou.solve(pid, N, par, x0[1], prob.initial_guess())
-    np.testing.assert_array_equal(res["thread"][0][1], uo); np.testing.assert_array_equal(res["thread"][1][1], yo)
-    assert int(so["status"]) == res["thread"][2]["status"][1] and int(so["inner_iterations"]) == res["thread"][2]["inner_iterations"][1]
+
+
+def test_full_solve_at_the_largest_horizon(pb):
+    """One uncapped ALM+PANTR solve at N = 120 (the reference itself stops at N = 60, problems/CMakeLists.txt:33):
+    device vs oracle, bit for bit, for the nominal initial state and a perturbed one."""
+    name, pid, N = "realistic_quadcopter", 6, 120
+    solver, _ = pb.make_solver(pb.benchmark_options(name))
+    prob = pb.BatchedProblem(name, N)
+    x0 = np.tile(prob.initial_state(), (2, 1)); x0[1] += 0.01 * np.random.default_rng(120).standard_normal(9)
+    u = np.tile(prob.initial_guess(), (2, 1)); y = np.zeros((2, prob.m))
+    st = solver(prob, u, y, x0=x0)
+    par = ou.pack_params(solver)
+    for b in range(2):
+        uo, yo, so, _ = ou.solve(pid, N, par, x0[b], prob.initial_guess())
+        assert int(so["status"]) == st["status"][b]
+        assert int(so["inner_iterations"]) == st["inner_iterations"][b] and int(so["outer_iterations"]) == st["outer_iterations"][b]
+        np.testing.assert_array_equal(u[b], uo); np.testing.assert_array_equal(y[b], yo)
+    assert st["status"][0] == 1
 
 
 def _run_driver(pb, tmp_path, monkeypatch, name, N, extra):
@@ -106,7 +122,7 @@ def _run_driver(pb, tmp_path, monkeypatch, name, N, extra):
 
 def test_quadcopter_closed_loop_cold_start_matches_oracle(pb, tmp_path, monkeypatch):
     """warm=0 branch of the driver (mpc-driver.cpp:192-197) with general constraints: u and y are reset every step."""
-    name, pid, N, num_sim = "quadcopter", 1, 8, 3
+    name, pid, N, num_sim = "quadcopter", 5, 8, 3
     res, opts = _run_driver(pb, tmp_path, monkeypatch, name, N, [f"num_sim={num_sim}", "warm=0", "batch=2"])
     assert res["ncon"] == 4 * N + 4 and res["states"].shape == (9, num_sim + 1)
     solver, _ = pb.make_solver(opts)

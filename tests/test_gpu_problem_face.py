@@ -6,7 +6,8 @@ import pytest
 import oracle_util as ou
 
 pytestmark = pytest.mark.gpu
-PROBLEMS = [("hanging_chain", 0), ("quadcopter", 1), ("realistic_quadcopter", 2)]
+# oracle ids of the formulations the device runs: 5 / 6 = the condensed quadcopters (oracle/quadcopter_condensed.hpp)
+PROBLEMS = [("hanging_chain", 0), ("quadcopter", 5), ("realistic_quadcopter", 6)]
 
 
 @pytest.fixture(scope="module")
