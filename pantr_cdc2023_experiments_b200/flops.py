@@ -25,13 +25,62 @@ changes the algorithmic count.  (Until r01_v3 the count included the in-call rec
 """
 
 
+_GEN = None
+
+
+def _gen_counts():
+    """Exact operation counts of the sympy-generated model functions (tools/gen_models.py writes them)."""
+    global _GEN
+    if _GEN is None:
+        import json
+        import os
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "generated", "flop_counts.json")) as fh:
+            _GEN = json.load(fh)
+    return _GEN
+
+
+def _quadcopter(N, ns):
+    """The two quadcopter models: one from-scratch evaluation of each function in the REFERENCE formulation
+    (rollout, discrete adjoint, forward-over-adjoint: what CasADi's AD generates and oracle/quadcopter.hpp restates),
+    built from the exact counts of the generated f_c / c functions (generated/flop_counts.json) plus the hand-written
+    RK4 / cost / augmented-Lagrangian arithmetic around them; sin and cos count 1 flop each.
+      rk4 step        4 (f_c + 6 sincos) + 3*18 (stage points) + 9*7 (combination)
+      stage cost 40, terminal cost 24 (incl. the accumulation)
+      AL terms        per constraint: div, add, fmin, fmax, sub, 2 mul, add = 8  -> 32 per node, + c(x), + 6 sincos at node N
+      adjoint step    4 vjp + c_vjp + 182 (stage weights 9 + 3*27, sums 9 + 3*13, gradient 8, node 36)
+      tangent step    4 jvp + 117
+      2nd-order step  4 vjp + 4 hvjp + c_hvjp + c_jvp + c_vjp + 238
+    The device runs the CONDENSED formulation of the same derivatives (csrc/quadcopter_condensed.cuh), which executes
+    more operations (13 unit tangents per step for the step Jacobians) in exchange for lane parallelism; the roofline
+    numerator stays the algorithmic count."""
+    g = _gen_counts()[ns]
+    fc, jvp, vjp, hvjp = g["fc"], g["fc_jvp"], g["fc_vjp"], g["fc_hvjp"]
+    con, cj, cv, ch = g["con"], g["con_jvp"], g["con_vjp"], g["con_hvjp"]
+    rk4 = 4 * (fc + 6) + 3 * 18 + 9 * 7
+    f = N * (rk4 + 40) + 24
+    al = (N + 1) * (con + 32) + 6 + 2
+    adj = (cv + 27) + N * (4 * vjp + cv + 182)
+    node2 = ch + cj + cv + 31
+    hvp = (N * rk4 + al + N * (4 * vjp + 90)          # stage points, multipliers, first-order adjoint stage weights
+           + N * (4 * jvp + 117) + node2 + N * (4 * vjp + 4 * hvjp + node2 + 207))
+    return {"f": f, "psi": f + al, "psi_grad_psi": f + al + adj, "grad_psi": f + al + adj, "hess_psi_prod": hvp}
+
+
+def quadcopter(N):
+    return _quadcopter(N, "quadcopter_gen")
+
+
+def realistic_quadcopter(N):
+    return _quadcopter(N, "realistic_quadcopter_gen")
+
+
 def hanging_chain(N):
     f = 1915 * N + 124
     adj = 1904 * N + 33
     return {"f": f, "psi": f, "psi_grad_psi": f + adj, "grad_psi": f + adj, "hess_psi_prod": 8829 * N + 63}
 
 
-MODELS = {"hanging_chain": hanging_chain}
+MODELS = {"hanging_chain": hanging_chain, "quadcopter": quadcopter, "realistic_quadcopter": realistic_quadcopter}
 
 
 def solve_flops(problem_name, N, stats):

@@ -17,18 +17,21 @@ def shard_range(B: int, rank: int, world: int):
 
 def gather_stats(local_stats: np.ndarray, world: int, group=None):
     """Final per-instance stats gather (the only inter-rank traffic of a sharded solve): returns the
-    concatenation over ranks on every rank.  Works with any torch.distributed backend."""
+    concatenation over ranks on every rank.  gloo gathers host tensors; NCCL only moves device memory, so under
+    an NCCL group the bytes are staged through the current CUDA device."""
     if world == 1:
         return local_stats
     import torch
     import torch.distributed as dist
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
     raw = np.ascontiguousarray(local_stats).view(np.uint8).reshape(-1)
-    sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
-    dist.all_gather(sizes, torch.tensor([raw.size], dtype=torch.int64), group=group)
-    mx = int(max(int(s.item()) for s in sizes))
-    buf = torch.zeros(mx, dtype=torch.uint8)
-    buf[:raw.size] = torch.from_numpy(raw.copy())
-    out = [torch.zeros(mx, dtype=torch.uint8) for _ in range(world)]
+    sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(sizes, torch.tensor([raw.size], dtype=torch.int64, device=dev), group=group)
+    sizes = [int(s.item()) for s in sizes]
+    mx = max(sizes)
+    buf = torch.zeros(mx, dtype=torch.uint8, device=dev)
+    buf[:raw.size] = torch.from_numpy(raw.copy()).to(dev)
+    out = [torch.zeros(mx, dtype=torch.uint8, device=dev) for _ in range(world)]
     dist.all_gather(out, buf, group=group)
-    parts = [o.numpy()[:int(s.item())].view(local_stats.dtype) for o, s in zip(out, sizes)]
+    parts = [o.cpu().numpy()[:sz].view(local_stats.dtype) for o, sz in zip(out, sizes)]
     return np.concatenate(parts)
