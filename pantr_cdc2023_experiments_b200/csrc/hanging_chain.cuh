@@ -597,6 +597,7 @@ struct HangingChain {
 #ifndef PANTR_MIN_BLOCKS
 #define PANTR_MIN_BLOCKS 12 // resident warps per SM the solve kernel is compiled for (168 registers)
 #endif
+    static constexpr bool HAS_ROLLOUT_TAG = false;
     static constexpr int MIN_BLOCKS = PANTR_MIN_BLOCKS;
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int) { return 0; }

@@ -76,6 +76,7 @@
         t_inner_start = globaltimer_ns();
         res = InnerResult{PANTR_B200_BUSY, INFINITY, 0};
         s.always_overwrite = always_overwrite; s.has_errz = has_errz;
+        if constexpr (Model::HAS_ROLLOUT_TAG) mdl.untag(); // the iterate slots are about to be overwritten
         xcopy<E>(X + curr * n, x, n); // pantr.tpp:195
         E::sync();
         // ---- initial Lipschitz estimate: pantr.tpp:200-217, panoc-helpers.tpp:288-334 ----
@@ -165,6 +166,7 @@
         // immediately overwrites the result with psi_grad_psi(prox.x): numerically dead, so only counted.
         if (!need_grad) ++st.ev_grad_L;
         xcopy<E>(X + prox * n, XH + curr * n, n);
+        if constexpr (Model::HAS_ROLLOUT_TAG) mdl.retag(XH + curr * n, X + prox * n); // psi(x_hat) rolled this very point out
         double cg_ = it[curr].gamma, cL_ = it[curr].L, cpsi = it[curr].psi_xh;
         E::sync();
         it[prox].gamma = cg_; it[prox].L = cL_; it[prox].psi_x = cpsi;

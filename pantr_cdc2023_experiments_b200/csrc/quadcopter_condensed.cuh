@@ -25,10 +25,16 @@
 // operation order on the CPU (bit-identical results), oracle/quadcopter.hpp is the reference
 // formulation (agreement to rounding, tests/test_oracle_quadcopter.py).
 //
-// Per-instance model workspace (global memory; L2-resident for the resident warps):
-//   traj (N+1) x 9 | sc (4N+1) x 6 sin/cos of every stage point | AB N x 13 x 9 (column-major) |
-//   lam (N+1) x 9 adjoint states | yh, wact 4(N+1) | dtraj (N+1) x 9 tangent states |
-//   mus (N+1) x 9 and usrc N x 4: per-step sources (then states) of the second-order adjoint recurrence
+// Per-instance model workspace (global memory):
+//   AB N x 118 (13 columns x 9 rows + pad: 944 bytes per step) | lam, mus (N+1) x 14 rows
+//   [x-part source -> adjoint state (9) | u-part addend (4) | pad] of the two adjoint recurrences |
+//   traj, dtraj (N+1) x 9 | sc (4N+1) x 6 sin/cos of every stage point | yh, wact 4(N+1)
+// The three recurrences are latency chains: every operand of a step must already sit in shared memory when the
+// step starts.  Each step's record (AB_k, and the source row of the adjoint recurrences) is therefore fetched
+// STEP_RING_DEPTH steps ahead by ONE elected lane with cp.async.bulk (TMA, 16-byte aligned 944 + 112 byte copies,
+// SASS: UBLKCP) completing on a per-slot mbarrier the warp waits on; results leave with plain stores.  (First
+// version, register prefetch one step ahead + global loads of the source rows: ~2000 cycles per step with the
+// resident warps' working set streaming from HBM, profiles/r02_a_quad_condensed_speed_v0.log.)
 #pragma once
 #include "pantr_hd.h"
 #include "generated/quadcopter_gen.h"
@@ -89,6 +95,55 @@ __device__ __forceinline__ void ldv(const double *p, double *out) {
 
 } // namespace qc
 
+// ---- per-step record ring of the matrix-vector recurrences: cp.async.bulk + mbarrier ----
+#ifndef PANTR_QC_RING_DEPTH
+#define PANTR_QC_RING_DEPTH 4
+#endif
+namespace qc {
+constexpr int ABS = 118;  // doubles per step of AB (117 + 1: bulk copies move multiples of 16 bytes)
+constexpr int ROW = 14;   // doubles per row of lam / mus
+constexpr int RING_D = PANTR_QC_RING_DEPTH, RING_SLOT = ABS + ROW;
+struct StepRing {
+    double *slot;              // RING_D x RING_SLOT
+    double *xch;               // 2 x 16: the recurrence's state / operand exchange (ping-pong)
+    unsigned long long *bar;   // RING_D mbarriers
+};
+/// One shared-memory ring per block, shared by the three recurrences (they never overlap in time).
+__device__ __noinline__ StepRing step_ring() {
+    __shared__ __align__(16) double storage[RING_D * RING_SLOT + 32];
+    __shared__ __align__(8) unsigned long long bars[RING_D];
+    return StepRing{storage, storage + RING_D * RING_SLOT, bars};
+}
+__device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+/// orders this thread's (and, after a __syncwarp, the warp's) generic-proxy accesses -- the rows / AB written with plain
+/// stores to global memory, the reads of a ring slot about to be refilled -- before its following async-proxy copies
+__device__ __forceinline__ void proxy_async_fence() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+/// global -> shared bulk copy (TMA), bytes a multiple of 16, both addresses 16-byte aligned; completes on `bar`
+__device__ __forceinline__ void bulk_g2s(double *dst, const double *src, unsigned bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "WAIT_%=:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra DONE_%=;\n"
+                 "bra WAIT_%=;\n"
+                 "DONE_%=:\n"
+                 "}" ::"r"(smem_addr(bar)), "r"(parity)
+                 : "memory");
+}
+} // namespace qc
+
 #ifndef PANTR_QC_MIN_BLOCKS
 #define PANTR_QC_MIN_BLOCKS 16 // resident warps per SM the solve kernel is compiled for (128 registers)
 #endif
@@ -102,7 +157,7 @@ struct QuadCondensedModel {
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int N) { return NC * (N + 1); }
     __host__ __device__ static int traj_doubles(int N) {
-        const int d = 4 * (N + 1) * NX + (4 * N + 1) * 6 + N * NZ * NX + 2 * NC * (N + 1) + N * NU;
+        const int d = N * qc::ABS + 2 * (N + 1) * qc::ROW + 2 * (N + 1) * NX + (4 * N + 1) * 6 + 2 * NC * (N + 1);
         return (d + 1) / 2 * 2; // the solver vectors behind it stay 16-byte aligned
     }
     __host__ __device__ static double C_lb(int i) { return (i & 3) == 0 ? 0.0 : -qc::dtilt_max; } // quadcopter.py:56-59, ss.py:28-29
@@ -121,15 +176,24 @@ struct QuadCondensedModel {
 
     int N;
     const double *x0;
-    double *traj, *sc, *AB, *lam, *yh, *wact, *dtraj, *mus, *usrc;
+    double *traj, *sc, *AB, *lam, *yh, *wact, *dtraj, *mus;
     bool hvp_ready;
+    /// The vector whose rollout traj / sc currently hold.  PANTR evaluates psi(x_hat) and then, one step later,
+    /// psi_grad_psi at a copy of the same point (pantr.tpp:303-316: prox.x = curr.x_hat): the solver moves the tag
+    /// along with the copy (retag) and eval_psi_grad_psi skips the second rollout -- same values, a third fewer
+    /// sequential sweeps.  Every rollout sets the tag, only eval_psi_grad_psi ever trusts it.
+    const double *rolled;
+    static constexpr bool HAS_ROLLOUT_TAG = true;
+    __device__ __forceinline__ void retag(const double *from, const double *to) { if (rolled == from) rolled = to; }
+    __device__ __forceinline__ void untag() { rolled = nullptr; }
 
     __device__ void init(int N_, const double *x0_, double *ws) {
-        N = N_; x0 = x0_; hvp_ready = false;
+        N = N_; x0 = x0_; hvp_ready = false; rolled = nullptr;
         double *p = ws;
-        traj = p; p += (N + 1) * NX; lam = p; p += (N + 1) * NX; dtraj = p; p += (N + 1) * NX; mus = p; p += (N + 1) * NX;
-        sc = p; p += (4 * N + 1) * 6; AB = p; p += N * NZ * NX; yh = p; p += NC * (N + 1); wact = p; p += NC * (N + 1);
-        usrc = p;
+        // the bulk-copied arrays first: the block's workspace starts 128-byte aligned, AB steps are 944 bytes, rows 112
+        AB = p; p += N * qc::ABS; lam = p; p += (N + 1) * qc::ROW; mus = p; p += (N + 1) * qc::ROW;
+        traj = p; p += (N + 1) * NX; dtraj = p; p += (N + 1) * NX;
+        sc = p; p += (4 * N + 1) * 6; yh = p; p += NC * (N + 1); wact = p;
     }
 
     // ---- one RK4 step (quadcopter.py:49-55), executed by every lane; the sin/cos of the three angles of a
@@ -164,18 +228,22 @@ struct QuadCondensedModel {
     }
     /// Rollout (ss.py:24): fills traj and sc.
     __device__ __noinline__ void rollout(const double *u) {
-        double x[NX], uk[NU];
+        double x[NX], uk[NU], un[NU];
 #pragma unroll
         for (int i = 0; i < NX; ++i) { x[i] = x0[i]; traj[i] = x[i]; }
+        qc::ldv<NU>(u, un);
 #pragma unroll 1
         for (int k = 0; k < N; ++k) {
-            qc::ldv<NU>(u + NU * k, uk);
+#pragma unroll
+            for (int j = 0; j < NU; ++j) uk[j] = un[j];
+            qc::ldv<NU>(u + NU * (k + 1 < N ? k + 1 : k), un); // the next step's input travels while this step computes
             rk4_step(x, uk, sc + 24 * k);
 #pragma unroll
             for (int i = 0; i < NX; ++i) traj[(k + 1) * NX + i] = x[i];
         }
         double s6[6];
         stage_sincos(x, s6, sc + 24 * N);
+        rolled = u;
         __syncwarp();
     }
     /// Cost (ss.py:32-36): lane = node, node k < N contributes l(x_k, u_k), node N contributes l_N(x_N).
@@ -275,7 +343,7 @@ struct QuadCondensedModel {
 #pragma unroll
             for (int i = 0; i < NZ; ++i) e[i] = i == c ? 1.0 : 0.0;
             step_tangent(xk, uk, s, e, e + NX, out);
-            double *col = AB + (size_t(k) * NZ + c) * NX;
+            double *col = AB + size_t(k) * qc::ABS + c * NX;
 #pragma unroll
             for (int i = 0; i < NX; ++i) col[i] = out[i];
         }
@@ -284,102 +352,133 @@ struct QuadCondensedModel {
             const int ncopy = (N - 1) * NCST * NX;
             for (int t = lane_id(); t < ncopy; t += 32) {
                 const int k = 1 + t / (NCST * NX), r = t % (NCST * NX), c = nth_col(F::CONST_COLS, r / NX), i = r % NX;
-                AB[(size_t(k) * NZ + c) * NX + i] = AB[size_t(c) * NX + i];
+                AB[size_t(k) * qc::ABS + c * NX + i] = AB[c * NX + i];
             }
         }
         __syncwarp();
     }
-    /// Adjoint recurrence w_k = AB_k' w_{k+1} + src_k over k = N-1..0 (lane c < 13 owns entry c of the
-    /// product: one fma chain over the 9 rows; the 9 adjoint entries travel through shared memory).
-    /// state: [(N+1) x 9], row N = terminal value (in), rows 1..N-1 hold the x-part sources on entry and the
-    ///        adjoint states on exit (row 0 is not needed: x_0 does not depend on u).
-    /// The u-part of step k, combined with the addend `ufun` supplies, goes to out[4k + j].
-    template <class UFun>
-    __device__ __forceinline__ void adjoint_recurrence(double *state, double *out, UFun ufun) {
-        __shared__ double wbuf[2][16];
+    /// Adjoint recurrence w_k = AB_k' w_{k+1} + src_k over k = N-1..0 (lane c < 13 owns entry c of the product: one
+    /// fma chain over the 9 rows; the 9 adjoint entries travel through shared memory).
+    /// rows: [(N+1) x ROW]; row N = terminal value (in); row k < N holds the x-part source (entries 0..8) and the
+    /// u-part addend (9..12) on entry, the adjoint state lambda_k in 0..8 on exit (row 0 keeps its source: x_0 does
+    /// not depend on u).  The u-part of step k, combined with its addend by `fin`, goes to out[4k + j].
+    /// Step i (k = N-1-i) reads its record -- AB_k and row k -- from ring slot i % D, filled D steps earlier.
+    template <class Fin>
+    __device__ __forceinline__ void adjoint_recurrence(double *rows, double *out, Fin fin) {
+        using namespace qc;
+        const StepRing R = step_ring();
         const int lane = lane_id();
-        int cur = 0;
-        if (lane < NX) wbuf[0][lane] = state[N * NX + lane];
-        double col[NX], ncol[NX];
         const int cl = lane < NZ ? lane : NZ - 1;
-        qc::ldv<NX>(AB + (size_t(N - 1) * NZ + cl) * NX, col);
-        __syncwarp();
+        auto issue = [&](int i) { // lane 0 only
+            const int k = N - 1 - i, sl = i % RING_D;
+            double *dst = R.slot + sl * RING_SLOT;
+            mbar_expect_tx(R.bar + sl, (ABS + ROW) * 8);
+            bulk_g2s(dst, AB + size_t(k) * ABS, ABS * 8, R.bar + sl);
+            bulk_g2s(dst + ABS, rows + size_t(k) * ROW, ROW * 8, R.bar + sl);
+        };
+        if (lane == 0) {
+#pragma unroll
+            for (int sl = 0; sl < RING_D; ++sl) mbar_init(R.bar + sl, 1);
+            mbar_init_fence();
+        }
+        if (lane < NX) R.xch[lane] = rows[N * ROW + lane];
+        __syncwarp(); // also orders the sources the lanes wrote to `rows` before lane 0's bulk reads
+        if (lane == 0) {
+            proxy_async_fence();
+            for (int i = 0; i < RING_D && i < N; ++i) issue(i);
+        }
+        int cur = 0;
 #pragma unroll 1
-        for (int k = N - 1; k >= 0; --k) {
-            double addend = 0;
-            if (lane < NX) { if (k > 0) addend = state[k * NX + lane]; }
-            else if (lane < NZ) addend = ufun(k, lane - NX);
-            if (k > 0) qc::ldv<NX>(AB + (size_t(k - 1) * NZ + cl) * NX, ncol);
-            double w[NX];
-            qc::ldv<NX>(wbuf[cur], w);
+        for (int i = 0; i < N; ++i) {
+            const int k = N - 1 - i, sl = i % RING_D;
+            mbar_wait(R.bar + sl, (i / RING_D) & 1);
+            const double *rec = R.slot + sl * RING_SLOT;
+            double col[NX], w[NX];
+            ldv<NX>(rec + cl * NX, col);
+            const double addend = rec[ABS + cl];
+            ldv<NX>(R.xch + 16 * cur, w);
             double a = col[0] * w[0];
 #pragma unroll
             for (int r = 1; r < NX; ++r) a = fma(col[r], w[r], a);
             if (lane < NX) {
-                if (k > 0) { const double l = a + addend; state[k * NX + lane] = l; wbuf[cur ^ 1][lane] = l; }
-            } else if (lane < NZ) out[NU * k + lane - NX] = ufun.finish(lane - NX, a, addend);
-#pragma unroll
-            for (int r = 0; r < NX; ++r) col[r] = ncol[r];
+                if (k > 0) { const double l = a + addend; rows[k * ROW + lane] = l; R.xch[16 * (cur ^ 1) + lane] = l; }
+            } else if (lane < NZ) out[NU * k + lane - NX] = fin(lane - NX, a, addend);
             __syncwarp();
+            if (lane == 0 && i + RING_D < N) { proxy_async_fence(); issue(i + RING_D); }
             cur ^= 1;
         }
     }
-    struct GradU { // u-part of the gradient: fma(s * 2 w_u, u_kj, AB' lambda)
-        const double *u; double cs;
-        __device__ __forceinline__ double operator()(int k, int j) const { return u[NU * k + j]; }
-        __device__ __forceinline__ double finish(int j, double a, double ukj) const { return fma(cs * (2 * qc::wu(j)), ukj, a); }
+    struct GradFin { // u-part of the gradient: fma(s * 2 w_u, u_kj, AB' lambda)
+        double cs;
+        __device__ __forceinline__ double operator()(int j, double a, double ukj) const { return fma(cs * (2 * qc::wu(j)), ukj, a); }
     };
-    struct SrcU { // u-part of the Hessian-vector product: AB' mu + usrc
-        const double *usrc;
-        __device__ __forceinline__ double operator()(int k, int j) const { return usrc[k * NU + j]; }
-        __device__ __forceinline__ double finish(int, double a, double s) const { return a + s; }
+    struct SrcFin { // u-part of the Hessian-vector product: AB' mu + source
+        __device__ __forceinline__ double operator()(int, double a, double s) const { return a + s; }
     };
     /// Gradient of  s f + yh' g  wrt u (s = cost_scale); leaves lambda_1..N in lam.
     __device__ __noinline__ void adjoint(const double *u, double cost_scale, double *grad) {
         using namespace qc;
-        for (int k = 1 + lane_id(); k <= N; k += 32) { // node sources q_k = s dl/dx + J_c' yh_k
+        for (int k = lane_id(); k <= N; k += 32) { // rows of the recurrence: node sources q_k = s dl/dx + J_c' yh_k, and u_k
+            if (k < N) {
+#pragma unroll
+                for (int j = 0; j < NU; ++j) lam[k * ROW + NX + j] = u[NU * k + j];
+            }
+            if (k == 0) continue;
             double x[NX], s6[6], y4[NC], ax[NX];
             ldv<NX>(traj + k * NX, x); ldv<6>(sc + 24 * k, s6); ldv<NC>(yh + NC * k, y4);
             F::con_vjp(x, s6, y4, ax);
 #pragma unroll
             for (int i = 0; i < NX; ++i) {
                 const double dl = (2 * wx(i, k == N)) * (i < 3 ? x[i] - pf(i) : x[i]);
-                lam[k * NX + i] = fma(cost_scale, dl, ax[i]);
+                lam[k * ROW + i] = fma(cost_scale, dl, ax[i]);
             }
         }
         __syncwarp();
-        adjoint_recurrence(lam, grad, GradU{u, cost_scale});
+        adjoint_recurrence(lam, grad, GradFin{cost_scale});
     }
-    /// Tangent recurrence dx_{k+1} = AB_k (dx_k, v_k): lane r < 9 owns row r, one fma chain over the 13 columns.
+    /// Tangent recurrence dx_{k+1} = AB_k (dx_k, v_k): lane r < 9 owns row r, one fma chain over the 13 columns;
+    /// AB_k arrives through the ring, (dx_k, v_k) through the exchange buffer.
     __device__ __noinline__ void tangent(const double *v) {
-        __shared__ double zbuf[2][16];
+        using namespace qc;
+        const StepRing R = step_ring();
         const int lane = lane_id();
         const int rl = lane < NX ? lane : NX - 1;
-        int cur = 0;
-        if (lane < NX) { zbuf[0][lane] = 0.0; dtraj[lane] = 0.0; }
-        if (lane < NU) zbuf[0][NX + lane] = v[lane];
-        double row[NZ], nrow[NZ];
+        auto issue = [&](int k) { // lane 0 only
+            const int sl = k % RING_D;
+            mbar_expect_tx(R.bar + sl, ABS * 8);
+            bulk_g2s(R.slot + sl * RING_SLOT, AB + size_t(k) * ABS, ABS * 8, R.bar + sl);
+        };
+        if (lane == 0) {
 #pragma unroll
-        for (int c = 0; c < NZ; ++c) row[c] = AB[size_t(c) * NX + rl];
+            for (int sl = 0; sl < RING_D; ++sl) mbar_init(R.bar + sl, 1);
+            mbar_init_fence();
+        }
+        if (lane < NX) { R.xch[lane] = 0.0; dtraj[lane] = 0.0; }
+        if (lane < NU) R.xch[NX + lane] = v[lane];
         __syncwarp();
+        if (lane == 0) {
+            proxy_async_fence();
+            for (int k = 0; k < RING_D && k < N; ++k) issue(k);
+        }
+        int cur = 0;
 #pragma unroll 1
         for (int k = 0; k < N; ++k) {
+            const int sl = k % RING_D;
             double vn = 0;
-            if (k + 1 < N) {
-                if (lane < NU) vn = v[NU * (k + 1) + lane];
+            if (k + 1 < N && lane < NU) vn = v[NU * (k + 1) + lane];
+            mbar_wait(R.bar + sl, (k / RING_D) & 1);
+            const double *rec = R.slot + sl * RING_SLOT;
+            double row[NZ], z[NZ];
 #pragma unroll
-                for (int c = 0; c < NZ; ++c) nrow[c] = AB[(size_t(k + 1) * NZ + c) * NX + rl];
-            }
-            double z[NZ];
-            qc::ldv<NZ>(zbuf[cur], z);
+            for (int c = 0; c < NZ; ++c) row[c] = rec[c * NX + rl];
+            ldv<NZ>(R.xch + 16 * cur, z);
             double a = row[0] * z[0];
 #pragma unroll
             for (int c = 1; c < NZ; ++c) a = fma(row[c], z[c], a);
-            if (lane < NX) { dtraj[(k + 1) * NX + lane] = a; zbuf[cur ^ 1][lane] = a; }
-            if (lane < NU) zbuf[cur ^ 1][NX + lane] = vn;
-#pragma unroll
-            for (int c = 0; c < NZ; ++c) row[c] = nrow[c];
+            if (lane < NX) { dtraj[(k + 1) * NX + lane] = a; R.xch[16 * (cur ^ 1) + lane] = a; }
+            if (lane < NU) R.xch[16 * (cur ^ 1) + NX + lane] = vn;
             __syncwarp();
+            if (lane == 0 && k + RING_D < N) { proxy_async_fence(); issue(k + RING_D); }
             cur ^= 1;
         }
     }
@@ -398,8 +497,8 @@ struct QuadCondensedModel {
         for (int i = 0; i < NX; ++i) out[i] = fma(cost_scale * (2 * wx(i, k == N)), dx[i], bx[i]) + ax[i];
     }
     /// Per-step sources of the second-order adjoint recurrence, lane = step:
-    /// mus_k = d/dx_k[J_step' lambda_{k+1}] (dx_k, v_k) + node term of node k (k >= 1; row N = terminal node term),
-    /// usrc_k = d/du_k[...] (dx_k, v_k) + s 2 w_u v_k.
+    /// row k of mus = [ d/dx_k[J_step' lambda_{k+1}] (dx_k, v_k) + node term of node k (k >= 1; row N = terminal node term) |
+    ///                  d/du_k[...] (dx_k, v_k) + s 2 w_u v_k ].
     __device__ __noinline__ void second_order_sources(const double *u, const double *v, double cost_scale) {
         using namespace qc;
         for (int k = lane_id(); k <= N; k += 32) {
@@ -407,13 +506,13 @@ struct QuadCondensedModel {
                 double nd[NX];
                 node_second_order(N, cost_scale, nd);
 #pragma unroll
-                for (int i = 0; i < NX; ++i) mus[N * NX + i] = nd[i];
+                for (int i = 0; i < NX; ++i) mus[N * ROW + i] = nd[i];
                 continue;
             }
             double xk[NX], uk[NU], vk[NU], dx[NX], l[NX];
             const double *s = sc + 24 * k;
             ldv<NX>(traj + k * NX, xk); ldv<NU>(u + NU * k, uk); ldv<NU>(v + NU * k, vk);
-            ldv<NX>(dtraj + k * NX, dx); ldv<NX>(lam + (k + 1) * NX, l);
+            ldv<NX>(dtraj + k * NX, dx); ldv<NX>(lam + (k + 1) * ROW, l);
             double s1[6], s2[6], s3[6], s4[6];
             ldv<6>(s, s1); ldv<6>(s + 6, s2); ldv<6>(s + 12, s3); ldv<6>(s + 18, s4);
             // tangent stage points
@@ -466,14 +565,14 @@ struct QuadCondensedModel {
                 double nd[NX];
                 node_second_order(k, cost_scale, nd);
 #pragma unroll
-                for (int i = 0; i < NX; ++i) mus[k * NX + i] = sx[i] + nd[i];
+                for (int i = 0; i < NX; ++i) mus[k * ROW + i] = sx[i] + nd[i];
             }
 #pragma unroll
-            for (int j = 0; j < NU; ++j) usrc[k * NU + j] = fma(cost_scale * (2 * wu(j)), vk[j], su[j]);
+            for (int j = 0; j < NU; ++j) mus[k * ROW + NX + j] = fma(cost_scale * (2 * wu(j)), vk[j], su[j]);
         }
         __syncwarp();
     }
-    __device__ __noinline__ void mu_recurrence(double *Hv) { adjoint_recurrence(mus, Hv, SrcU{usrc}); }
+    __device__ __noinline__ void mu_recurrence(double *Hv) { adjoint_recurrence(mus, Hv, SrcFin{}); }
     /// Hv = hess(s f + AL terms)(u) v; needs the caches of the last gradient at u (AB, lam, yh, wact, sc, traj).
     __device__ __forceinline__ void hvp(const double *u, const double *v, double cost_scale, double *Hv) {
         tangent(v);
@@ -511,7 +610,7 @@ struct QuadCondensedModel {
     }
     __device__ __noinline__ double eval_psi_grad_psi(const double *x, const double *y, const double *S, double *grad) {
         __syncwarp();
-        rollout(x);
+        if (rolled != x) rollout(x);
         const double f = cost(x);
         const double psi = f + al_terms(y, S, yh, wact);
         gradient_caches(x, 1.0, grad);
