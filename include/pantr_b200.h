@@ -233,6 +233,15 @@ int pantr_b200_set_order_device(pantr_b200_solver *s, const int32_t *d_order, in
  * Automatic = 1.  A mode that does not apply to the model falls back to 1. */
 int pantr_b200_set_exec_mode(pantr_b200_solver *s, int mode);
 
+/* Own memory checks (the analogue of the reference's Debug-mode NaN poisoning of stale iterates, pantr.tpp:460-467, and
+ * of its sanitizer builds, alpaqa/cmake/Sanitizers.cmake:1-15).  flags: 1 = every double of the per-block workspace is
+ * set to NaN before each launch (a read of stale or uninitialised workspace then poisons the result: results must stay
+ * bit-identical), 2 = the 32-double guard band behind every block's workspace is filled with a canary before each
+ * launch; pantr_b200_check_guards counts the canaries that were overwritten since.  grid_limit > 0 caps the number of
+ * resident blocks of the solve kernel (results must not depend on it: blocks share nothing but the instance queue). */
+int pantr_b200_set_debug(pantr_b200_solver *s, int flags, int grid_limit);
+int pantr_b200_check_guards(pantr_b200_solver *s, int64_t *violations);
+
 /* Optional per-iteration trace of one instance of the next solve_batch call (debug / parity):
  * rows of 11 doubles {k, psi, fbe, gamma, eps, radius, rho, q_model, nJ, cg_iters, accepted}. */
 int pantr_b200_set_trace(pantr_b200_solver *s, int64_t instance, int max_rows);

@@ -66,7 +66,8 @@ SYMBOLS = [
     "pantr_b200_simulate_dynamics_batch", "pantr_b200_simulate_dynamics_batch_device",
     "pantr_b200_shift_warm_start_device", "pantr_b200_set_trace", "pantr_b200_get_trace",
     "pantr_b200_kernel_launches", "pantr_b200_grid_size", "pantr_b200_measure_fp64_peak",
-    "pantr_b200_last_error", "pantr_b200_set_exec_mode", "pantr_b200_set_order_device",
+    "pantr_b200_last_error", "pantr_b200_set_exec_mode", "pantr_b200_set_order_device", "pantr_b200_set_debug",
+    "pantr_b200_check_guards",
     # problem plugin face (alpaqa_problem_functions_t members, batched)
     "pantr_b200_eval_f_batch", "pantr_b200_eval_grad_f_batch", "pantr_b200_eval_f_grad_f_batch",
     "pantr_b200_eval_g_batch", "pantr_b200_eval_grad_g_prod_batch", "pantr_b200_eval_grad_L_batch",
@@ -116,6 +117,8 @@ def load():
     lib.pantr_b200_kernel_launches.restype = i64
     lib.pantr_b200_grid_size.argtypes = [vp]
     lib.pantr_b200_set_exec_mode.argtypes = [vp, C.c_int]
+    lib.pantr_b200_set_debug.argtypes = [vp, C.c_int, C.c_int]
+    lib.pantr_b200_check_guards.argtypes = [vp, C.POINTER(i64)]
     lib.pantr_b200_set_order_device.argtypes = [vp, vp, i64]
     lib.pantr_b200_measure_fp64_peak.argtypes = [C.c_int, C.c_int, dp]
     f64 = C.c_double

@@ -65,6 +65,15 @@ class BatchedProblem:
         self.n, self.m, self.nx, self.nu, self.nc = self._probe.dims
         self.x0 = None if x0 is None else _f64(x0, (np.shape(x0)[0], self.nx), "x0")
 
+    def set_debug(self, flags, grid_limit=0):
+        """Memory checks for the problem-function launches of this object (pantr_b200_set_debug)."""
+        _lib.check(_lib.load().pantr_b200_set_debug(self._probe.h, flags, grid_limit))
+
+    def check_guards(self):
+        bad = C.c_int64(-1)
+        _lib.check(_lib.load().pantr_b200_check_guards(self._probe.h, C.byref(bad)))
+        return bad.value
+
     # TypeErasedProblem::get_n / get_m / get_box_C / get_box_D
     def get_n(self): return self.n
     def get_m(self): return self.m
@@ -309,6 +318,16 @@ class ALMSolver:
         instance, forward-over-adjoint sweeps: quadcopters only, the round-1 path kept for A/B runs)."""
         code = {"auto": 0, "warp": 1, "thread": 2}[mode]
         _lib.check(_lib.load().pantr_b200_set_exec_mode(self._handle(problem).h, code))
+
+    def set_debug(self, problem, flags, grid_limit=0):
+        """flags: 1 = NaN-poison the workspace before every launch, 2 = guard bands (see check_guards)."""
+        _lib.check(_lib.load().pantr_b200_set_debug(self._handle(problem).h, flags, grid_limit))
+
+    def check_guards(self, problem):
+        """Number of guard-band doubles overwritten since the last launch (0 = no workspace overrun)."""
+        bad = C.c_int64(-1)
+        _lib.check(_lib.load().pantr_b200_check_guards(self._handle(problem).h, C.byref(bad)))
+        return bad.value
 
     def set_trace(self, problem, instance, max_rows=4096):
         _lib.check(_lib.load().pantr_b200_set_trace(self._handle(problem).h, instance, max_rows))
