@@ -76,11 +76,12 @@ def run(argv):
     num_sim = _get_opt(opts, used, "num_sim", horizon, int)
     warm = _get_opt(opts, used, "warm", True, _bool)
     record = min(B, _get_opt(opts, used, "record", 4, int))
+    batch_npz = _get_opt(opts, used, "batch_npz", B <= 4096, _bool)  # per-instance arrays of all B closed loops (large)
     _get_opt(opts, used, "results_name", None, str)
     unused = [o for o, u in zip(opts, used) if not u]
     if unused:                                                                 # mpc-driver.cpp:403-411
         print("Unused options:", " ".join(unused), file=sys.stderr)
-    print("u_dist =", " ".join(f"{v:g}" for v in u_dist))
+    print("u_dist =", " ".join(f"{v:g}" for v in u_dist), flush=True)
 
     import torch
     lib = _lib.load()
@@ -165,11 +166,11 @@ def run(argv):
           f"num var: {n}\nnum con: {m}\nbatch:   {B} closed loops x {num_sim} MPC steps\n"
           f"time: {total:.3f} s wall, {B * num_sim / max(wall.sum(), 1e-12):.1f} solves/s on device, "
           f"converged {100 * conv:.2f} %, mean PANTR iterations {iters.mean():.2f}, "
-          f"mean Hessian-vector products {evals['ev_hess_psi_prod'].sum() / (B * num_sim):.1f} per solve\n")
+          f"mean Hessian-vector products {evals['ev_hess_psi_prod'].sum() / (B * num_sim):.1f} per solve\n", flush=True)
     rname, ts = results_name(opts)
     extra = [("batch_size", B), ("batch_wall_time_per_step", wall), ("batch_converged_fraction", float(conv)),
              ("batch_mean_inner_iterations", float(iters.mean()))]
-    if B > 1:
+    if B > 1 and batch_npz:
         npz = rname + ".npz"
         np.savez_compressed(npz, runtimes=runtimes, states=states, inputs=inputs, first_inputs=first_inputs,
                             inner_iterations=iters, disturbance_inputs=dist,
