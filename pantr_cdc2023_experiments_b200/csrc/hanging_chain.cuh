@@ -207,6 +207,9 @@ __device__ __forceinline__ void stage_fetch(const Lane &L, double *buf, const do
 // values of 1/|dist| (a copy of the step's iwc block, so that one contiguous block feeds both sweeps of
 // the product).  Written by the adjoint sweep (depends on u only, like adjc); with it the product does
 // not rebuild the stage points (no state trajectory reads, no k_j chain, 8 shuffles fewer per stage).
+#ifndef PANTR_HC_TMA
+#define PANTR_HC_TMA 0 // 1: the per-step blocks of the product arrive by cp.async.bulk + mbarrier (one elected lane) instead of cp.async
+#endif
 #ifndef PANTR_HC_DIST_CACHE
 #define PANTR_HC_DIST_CACHE 1 // 0: the product rebuilds the stage points from traj + iwc (the r01_v9 kernel, kept for A/B runs)
 #endif
@@ -327,6 +330,9 @@ __device__ __noinline__ void adjoint(int N, const double *u, const double *traj,
         }
         X = Xp; V = Vp; ud = up; iw = iwp;
     }
+#if PANTR_HC_TMA
+    __threadfence(); // dic / adjc are read through the async proxy (TMA reads L2) by the products that follow
+#endif
 }
 
 // Hv = hess f(u) v by forward-over-adjoint (the exact Hessian-vector product that
@@ -508,6 +514,94 @@ __device__ __forceinline__ void hvjp_chain(const Lane &L, const Links &K, const 
     tX = tX + bX; tV = tV + bV;
 }
 
+#if PANTR_HC_TMA
+// Same product, same operands, same bits; only the transport of the per-step blocks differs: ONE lane issues one bulk
+// copy per block (dic 1280 B; reverse sweep also adjc 1280 B and the 464-byte tangent row) that completes on the slot's
+// mbarrier, instead of every lane issuing 2-5 16-byte cp.async plus commit / wait_group.
+__device__ __noinline__ void hvp(int N, const double *u, const double *v, const double *traj, double *dtraj,
+                                 const double *iwc, const double *adjc, const double *dic, double *Hv) {
+    (void)u; (void)traj; (void)iwc; // v, Hv may be shared memory
+    __builtin_assume(__isGlobal(dtraj)); __builtin_assume(__isGlobal(adjc)); __builtin_assume(__isGlobal(dic));
+    const Lane L;
+    constexpr int RSLOT = DSTEP + SCSTEP + DTS + 2; // reverse sweep: dic + adjc + dtraj row of one step (380 doubles)
+    __shared__ __align__(16) double ring[2 * RSLOT];
+    __shared__ __align__(8) unsigned long long bars[3];
+    double (*dring)[DSTEP] = reinterpret_cast<double (*)[DSTEP]>(ring); // forward sweep: 3 dic slots in the same bytes
+    static_assert(3 * DSTEP <= 2 * RSLOT, "ring");
+    const bool lead = lane_id() == 0;
+    double dX = 0.0, dV = 0.0;
+    // ---- forward tangent sweep: dic blocks two steps ahead through the 3-slot ring ----
+    dt_store(L, dtraj, 0, dX, dV);
+    if (lead) {
+        mbar_init(bars, 1); mbar_init(bars + 1, 1); mbar_init(bars + 2, 1);
+        mbar_init_fence();
+        for (int k = 0; k < 2 && k < N; ++k) { mbar_expect_tx(bars + k, DSTEP * 8); bulk_g2s(dring[k], dic + k * DSTEP, DSTEP * 8, bars + k); }
+    }
+    __syncwarp();
+    double vd = load_v(L, v, 0);
+    int s0 = 0, s2 = 2;
+    unsigned ph = 0; // bit j = parity of slot j's next completion
+#pragma unroll 1
+    for (int k = 0; k < N; ++k) {
+        mbar_wait(bars + s0, (ph >> s0) & 1u);
+        ph ^= 1u << s0;
+        __syncwarp(); // every lane has finished with slot s2 (read in step k - 1)
+        if (lead && k + 2 < N) { mbar_expect_tx(bars + s2, DSTEP * 8); bulk_g2s(dring[s2], dic + (k + 2) * DSTEP, DSTEP * 8, bars + s2); }
+        const double vp = load_v(L, v, k + 1 < N ? k + 1 : k);
+        Tan T; Links K; double kX[4], kV[4];
+        jvp_chain(L, dring[s0], dX, dV, vd, K, T, kX, kV);
+        dX = hcf::rk4c(dX, kX[0], kX[1], kX[2], kX[3]);
+        dV = hcf::rk4c(dV, kV[0], kV[1], kV[2], kV[3]);
+        dt_store(L, dtraj, k + 1, dX, dV);
+        vd = vp;
+        s0 = s0 == 2 ? 0 : s0 + 1; s2 = s2 == 2 ? 0 : s2 + 1;
+    }
+    __threadfence(); // the tangent rows are read back through the async proxy: they must have reached L2
+    __syncwarp();
+    // ---- reverse sweep for mu = d lambda ----
+    double mX = L.isEnd ? two_alpha * dX : 0.0;
+    double mV = L.hasV ? two_beta * dV : 0.0;
+    auto fetch = [&](int slot, int k) { // lead lane only
+        double *b = ring + slot * RSLOT;
+        mbar_expect_tx(bars + slot, (DSTEP + SCSTEP + DTS) * 8);
+        bulk_g2s(b, dic + k * DSTEP, DSTEP * 8, bars + slot);
+        bulk_g2s(b + DSTEP, adjc + k * SCSTEP, SCSTEP * 8, bars + slot);
+        bulk_g2s(b + DSTEP + SCSTEP, dtraj + k * DTS, DTS * 8, bars + slot);
+    };
+    if (lead) {
+        mbar_init(bars, 1); mbar_init(bars + 1, 1);
+        mbar_init_fence();
+        fetch(0, N - 1);
+    }
+    __syncwarp();
+    vd = load_v(L, v, N - 1);
+    int cur = 0;
+    ph = 0;
+#pragma unroll 1
+    for (int k = N - 1; k >= 0; --k) {
+        mbar_wait(bars + cur, (ph >> cur) & 1u);
+        ph ^= 1u << cur;
+        __syncwarp(); // every lane has finished with the other slot (read in the previous step)
+        const double *db = ring + cur * RSLOT, *ab = db + DSTEP, *tb = ab + SCSTEP;
+        if (lead && k > 0) fetch(cur ^ 1, k - 1);
+        cur ^= 1;
+        const double vp = load_v(L, v, k > 0 ? k - 1 : 0);
+        dX = tb[L.l];                      // lanes 30, 31 / 27..29: unused garbage (see above)
+        dV = tb[L.l < NVL ? NL + L.l : 0];
+        Tan T; Links K; double kX[4], kV[4], tX, tV;
+        jvp_chain(L, db, dX, dV, vd, K, T, kX, kV);
+        hvjp_chain(L, K, ab, T, mX, mV, tX, tV);
+        mX = L.isEnd ? fma(two_alpha, dX, tX) : tX;
+        if (L.hasV) mV = fma(two_beta, dV, tV);
+        else {
+            if (L.isEnd) Hv[NU * k + (L.l - NVL)] = fma(two_gamma, vd, tV);
+            mV = 0.0;
+        }
+        vd = vp;
+    }
+    __syncwarp();
+}
+#else
 __device__ __noinline__ void hvp(int N, const double *u, const double *v, const double *traj, double *dtraj,
                                  const double *iwc, const double *adjc, const double *dic, double *Hv) {
     (void)u; (void)traj; (void)iwc; // v, Hv may be shared memory
@@ -587,6 +681,7 @@ __device__ __noinline__ void hvp(int N, const double *u, const double *v, const 
     cp_async_wait_all();
     __syncwarp();
 }
+#endif
 #endif
 
 } // namespace hc

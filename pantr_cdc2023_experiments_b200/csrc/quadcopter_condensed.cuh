@@ -26,15 +26,20 @@
 // formulation (agreement to rounding, tests/test_oracle_quadcopter.py).
 //
 // Per-instance model workspace (global memory):
-//   AB N x 118 (13 columns x 9 rows + pad: 944 bytes per step) | lam, mus (N+1) x 14 rows
+//   AB N x 130 (13 columns x (9 rows + pad): 1040 bytes per step) | lam, mus (N+1) x 14 rows
 //   [x-part source -> adjoint state (9) | u-part addend (4) | pad] of the two adjoint recurrences |
 //   traj, dtraj (N+1) x 9 | sc (4N+1) x 6 sin/cos of every stage point | yh, wact 4(N+1)
 // The three recurrences are latency chains: every operand of a step must already sit in shared memory when the
-// step starts.  Each step's record (AB_k, and the source row of the adjoint recurrences) is therefore fetched
-// STEP_RING_DEPTH steps ahead by ONE elected lane with cp.async.bulk (TMA, 16-byte aligned 944 + 112 byte copies,
-// SASS: UBLKCP) completing on a per-slot mbarrier the warp waits on; results leave with plain stores.  (First
-// version, register prefetch one step ahead + global loads of the source rows: ~2000 cycles per step with the
-// resident warps' working set streaming from HBM, profiles/r02_a_quad_condensed_speed_v0.log.)
+// step starts.  A step's record is therefore fetched PANTR_QC_RING_DEPTH steps ahead into a shared-memory ring:
+// AB_k (1040 bytes) by ONE elected lane with cp.async.bulk (TMA; SASS: UBLKCP) completing on a per-slot mbarrier the
+// warp waits on; the 112-byte source row of the adjoint recurrences by cp.async (LDGSTS) of 7 lanes -- the rows are
+// written by the lanes just before the recurrence starts, and cp.async is a generic-proxy read ordered by
+// __syncwarp like any load, whereas a bulk copy of freshly written global data needs a gpu-scope fence first (AB gets
+// one __threadfence per build).  Results leave with plain stores.
+// History (profiles/): v0, register prefetch one step ahead + global loads of the source rows: ~2000 cycles per
+// step with the resident warps' working set streaming from HBM (r02_a_quad_condensed_speed_v0.log); v1, everything
+// by TMA with a fence.proxy.async before every refill: the fence alone cost as much (35-40 % of the recurrences'
+// stall samples on `membar`, r02_b_quadc_ncu_*).
 #pragma once
 #include "pantr_hd.h"
 #include "generated/quadcopter_gen.h"
@@ -100,9 +105,11 @@ __device__ __forceinline__ void ldv(const double *p, double *out) {
 #define PANTR_QC_RING_DEPTH 4
 #endif
 namespace qc {
-constexpr int ABS = 118;  // doubles per step of AB (117 + 1: bulk copies move multiples of 16 bytes)
-constexpr int ROW = 14;   // doubles per row of lam / mus
+constexpr int COL = 10;        // doubles per column of AB_k (9 + 1: columns start 16-byte aligned, LDS.128)
+constexpr int ABS = NZ * COL;  // doubles per step of AB (1040 bytes: bulk copies move multiples of 16 bytes)
+constexpr int ROW = 14;        // doubles per row of lam / mus (112 bytes)
 constexpr int RING_D = PANTR_QC_RING_DEPTH, RING_SLOT = ABS + ROW;
+static_assert((RING_D & (RING_D - 1)) == 0 && RING_D >= 2, "ring depth: a power of two");
 struct StepRing {
     double *slot;              // RING_D x RING_SLOT
     double *xch;               // 2 x 16: the recurrence's state / operand exchange (ping-pong)
@@ -113,34 +120,6 @@ __device__ __noinline__ StepRing step_ring() {
     __shared__ __align__(16) double storage[RING_D * RING_SLOT + 32];
     __shared__ __align__(8) unsigned long long bars[RING_D];
     return StepRing{storage, storage + RING_D * RING_SLOT, bars};
-}
-__device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-/// orders this thread's (and, after a __syncwarp, the warp's) generic-proxy accesses -- the rows / AB written with plain
-/// stores to global memory, the reads of a ring slot about to be refilled -- before its following async-proxy copies
-__device__ __forceinline__ void proxy_async_fence() { asm volatile("fence.proxy.async;" ::: "memory"); }
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
-}
-/// global -> shared bulk copy (TMA), bytes a multiple of 16, both addresses 16-byte aligned; completes on `bar`
-__device__ __forceinline__ void bulk_g2s(double *dst, const double *src, unsigned bytes, unsigned long long *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_addr(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
-    asm volatile("{\n"
-                 ".reg .pred p;\n"
-                 "WAIT_%=:\n"
-                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-                 "@p bra DONE_%=;\n"
-                 "bra WAIT_%=;\n"
-                 "DONE_%=:\n"
-                 "}" ::"r"(smem_addr(bar)), "r"(parity)
-                 : "memory");
 }
 } // namespace qc
 
@@ -343,7 +322,7 @@ struct QuadCondensedModel {
 #pragma unroll
             for (int i = 0; i < NZ; ++i) e[i] = i == c ? 1.0 : 0.0;
             step_tangent(xk, uk, s, e, e + NX, out);
-            double *col = AB + size_t(k) * qc::ABS + c * NX;
+            double *col = AB + size_t(k) * qc::ABS + c * qc::COL;
 #pragma unroll
             for (int i = 0; i < NX; ++i) col[i] = out[i];
         }
@@ -352,9 +331,10 @@ struct QuadCondensedModel {
             const int ncopy = (N - 1) * NCST * NX;
             for (int t = lane_id(); t < ncopy; t += 32) {
                 const int k = 1 + t / (NCST * NX), r = t % (NCST * NX), c = nth_col(F::CONST_COLS, r / NX), i = r % NX;
-                AB[size_t(k) * qc::ABS + c * NX + i] = AB[c * NX + i];
+                AB[size_t(k) * qc::ABS + c * qc::COL + i] = AB[c * qc::COL + i];
             }
         }
+        __threadfence(); // the recurrences read AB through the async proxy (TMA reads L2): the stores must have landed
         __syncwarp();
     }
     /// Adjoint recurrence w_k = AB_k' w_{k+1} + src_k over k = N-1..0 (lane c < 13 owns entry c of the product: one
@@ -369,12 +349,14 @@ struct QuadCondensedModel {
         const StepRing R = step_ring();
         const int lane = lane_id();
         const int cl = lane < NZ ? lane : NZ - 1;
-        auto issue = [&](int i) { // lane 0 only
-            const int k = N - 1 - i, sl = i % RING_D;
+        auto refill = [&](int i) { // record of step i -> slot i % D: AB by lane 0 (TMA), the row by lanes 0..6 (cp.async)
+            const int k = N - 1 - i, sl = i & (RING_D - 1);
             double *dst = R.slot + sl * RING_SLOT;
-            mbar_expect_tx(R.bar + sl, (ABS + ROW) * 8);
-            bulk_g2s(dst, AB + size_t(k) * ABS, ABS * 8, R.bar + sl);
-            bulk_g2s(dst + ABS, rows + size_t(k) * ROW, ROW * 8, R.bar + sl);
+            if (lane == 0) {
+                mbar_expect_tx(R.bar + sl, ABS * 8);
+                bulk_g2s(dst, AB + size_t(k) * ABS, ABS * 8, R.bar + sl);
+            }
+            if (lane < ROW / 2) cp_async_16(dst + ABS + 2 * lane, rows + size_t(k) * ROW + 2 * lane);
         };
         if (lane == 0) {
 #pragma unroll
@@ -382,19 +364,22 @@ struct QuadCondensedModel {
             mbar_init_fence();
         }
         if (lane < NX) R.xch[lane] = rows[N * ROW + lane];
-        __syncwarp(); // also orders the sources the lanes wrote to `rows` before lane 0's bulk reads
-        if (lane == 0) {
-            proxy_async_fence();
-            for (int i = 0; i < RING_D && i < N; ++i) issue(i);
+        __syncwarp(); // the rows the lanes have just written are ordered before the copies below
+#pragma unroll
+        for (int i = 0; i < RING_D; ++i) {
+            if (i < N) refill(i);
+            cp_async_commit_group();
         }
+        cp_async_wait_group<RING_D - 1>(); // step 0's row has landed ...
+        __syncwarp();                      // ... in every lane's view
         int cur = 0;
 #pragma unroll 1
         for (int i = 0; i < N; ++i) {
-            const int k = N - 1 - i, sl = i % RING_D;
+            const int k = N - 1 - i, sl = i & (RING_D - 1);
             mbar_wait(R.bar + sl, (i / RING_D) & 1);
             const double *rec = R.slot + sl * RING_SLOT;
             double col[NX], w[NX];
-            ldv<NX>(rec + cl * NX, col);
+            ldv<NX>(rec + cl * COL, col);
             const double addend = rec[ABS + cl];
             ldv<NX>(R.xch + 16 * cur, w);
             double a = col[0] * w[0];
@@ -403,10 +388,13 @@ struct QuadCondensedModel {
             if (lane < NX) {
                 if (k > 0) { const double l = a + addend; rows[k * ROW + lane] = l; R.xch[16 * (cur ^ 1) + lane] = l; }
             } else if (lane < NZ) out[NU * k + lane - NX] = fin(lane - NX, a, addend);
-            __syncwarp();
-            if (lane == 0 && i + RING_D < N) { proxy_async_fence(); issue(i + RING_D); }
+            cp_async_wait_group<RING_D - 2>(); // the next step's row has landed
+            __syncwarp();                      // slot `sl` has been read by every lane: refill it
+            if (i + RING_D < N) refill(i + RING_D);
+            cp_async_commit_group();
             cur ^= 1;
         }
+        cp_async_wait_group<0>();
     }
     struct GradFin { // u-part of the gradient: fma(s * 2 w_u, u_kj, AB' lambda)
         double cs;
@@ -443,8 +431,8 @@ struct QuadCondensedModel {
         const StepRing R = step_ring();
         const int lane = lane_id();
         const int rl = lane < NX ? lane : NX - 1;
-        auto issue = [&](int k) { // lane 0 only
-            const int sl = k % RING_D;
+        auto refill = [&](int k) { // lane 0 only
+            const int sl = k & (RING_D - 1);
             mbar_expect_tx(R.bar + sl, ABS * 8);
             bulk_g2s(R.slot + sl * RING_SLOT, AB + size_t(k) * ABS, ABS * 8, R.bar + sl);
         };
@@ -452,33 +440,30 @@ struct QuadCondensedModel {
 #pragma unroll
             for (int sl = 0; sl < RING_D; ++sl) mbar_init(R.bar + sl, 1);
             mbar_init_fence();
+            for (int k = 0; k < RING_D && k < N; ++k) refill(k);
         }
         if (lane < NX) { R.xch[lane] = 0.0; dtraj[lane] = 0.0; }
         if (lane < NU) R.xch[NX + lane] = v[lane];
         __syncwarp();
-        if (lane == 0) {
-            proxy_async_fence();
-            for (int k = 0; k < RING_D && k < N; ++k) issue(k);
-        }
         int cur = 0;
 #pragma unroll 1
         for (int k = 0; k < N; ++k) {
-            const int sl = k % RING_D;
+            const int sl = k & (RING_D - 1);
             double vn = 0;
             if (k + 1 < N && lane < NU) vn = v[NU * (k + 1) + lane];
             mbar_wait(R.bar + sl, (k / RING_D) & 1);
             const double *rec = R.slot + sl * RING_SLOT;
             double row[NZ], z[NZ];
 #pragma unroll
-            for (int c = 0; c < NZ; ++c) row[c] = rec[c * NX + rl];
+            for (int c = 0; c < NZ; ++c) row[c] = rec[c * COL + rl];
             ldv<NZ>(R.xch + 16 * cur, z);
             double a = row[0] * z[0];
 #pragma unroll
             for (int c = 1; c < NZ; ++c) a = fma(row[c], z[c], a);
             if (lane < NX) { dtraj[(k + 1) * NX + lane] = a; R.xch[16 * (cur ^ 1) + lane] = a; }
             if (lane < NU) R.xch[16 * (cur ^ 1) + NX + lane] = vn;
-            __syncwarp();
-            if (lane == 0 && k + RING_D < N) { proxy_async_fence(); issue(k + RING_D); }
+            __syncwarp(); // slot `sl` has been read by every lane: refill it
+            if (lane == 0 && k + RING_D < N) refill(k + RING_D);
             cur ^= 1;
         }
     }

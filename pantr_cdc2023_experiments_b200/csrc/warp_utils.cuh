@@ -23,6 +23,44 @@ __device__ __forceinline__ double shfl(double v, int src) {
     return __hiloint2double(hi, lo);
 }
 
+// ---- bulk asynchronous copies (TMA, cp.async.bulk) completing on a shared-memory mbarrier ----
+__device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_init_fence() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+/// orders this thread's (and, after a __syncwarp, the warp's) generic-proxy accesses -- the rows / AB written with plain
+/// stores to global memory, the reads of a ring slot about to be refilled -- before its following async-proxy copies
+__device__ __forceinline__ void proxy_async_fence() { asm volatile("fence.proxy.async;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+/// global -> shared bulk copy (TMA), bytes a multiple of 16, both addresses 16-byte aligned; completes on `bar`
+__device__ __forceinline__ void bulk_g2s(double *dst, const double *src, unsigned bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "WAIT_%=:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra DONE_%=;\n"
+                 "bra WAIT_%=;\n"
+                 "DONE_%=:\n"
+                 "}" ::"r"(smem_addr(bar)), "r"(parity)
+                 : "memory");
+}
+
+// ---- per-thread asynchronous copies (cp.async / LDGSTS: generic proxy, L2 -> shared) ----
+__device__ __forceinline__ void cp_async_16(double *smem, const double *g) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem)), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_group() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 __device__ __forceinline__ double warp_sum(double p) {
 #pragma unroll
     for (int m = 16; m >= 1; m >>= 1) p = p + __shfl_xor_sync(FULL, p, m);
