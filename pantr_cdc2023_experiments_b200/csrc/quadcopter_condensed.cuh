@@ -116,7 +116,7 @@ struct StepRing {
     unsigned long long *bar;   // RING_D mbarriers
 };
 /// One shared-memory ring per block, shared by the three recurrences (they never overlap in time).
-__device__ __noinline__ StepRing step_ring() {
+__device__ __forceinline__ StepRing step_ring() {
     __shared__ __align__(16) double storage[RING_D * RING_SLOT + 32];
     __shared__ __align__(8) unsigned long long bars[RING_D];
     return StepRing{storage, storage + RING_D * RING_SLOT, bars};
@@ -153,6 +153,16 @@ struct QuadCondensedModel {
         for (int k = 0; k < N; ++k) { u[4 * k] = 9.81; u[4 * k + 1] = u[4 * k + 2] = u[4 * k + 3] = 0; }
     }
 
+    // The model object lives in local memory (its methods are __noinline__ and take `this`), and every store through a
+    // double* may alias it: a sweep that reads N or an array pointer inside its loop reloads it from memory in every step
+    // (three exposed loads per recurrence step in the first version, profiles/r02_c_*).  Every sweep therefore starts by
+    // copying the members it uses into locals of the same name.
+#define PANTR_QC_LOCALS                                                                                                  \
+    const int N = this->N;                                                                                               \
+    const double *const x0 = this->x0;                                                                                   \
+    double *const traj = this->traj, *const sc = this->sc, *const AB = this->AB, *const lam = this->lam,                 \
+                  *const yh = this->yh, *const wact = this->wact, *const dtraj = this->dtraj, *const mus = this->mus;    \
+    (void)N; (void)x0; (void)traj; (void)sc; (void)AB; (void)lam; (void)yh; (void)wact; (void)dtraj; (void)mus
     int N;
     const double *x0;
     double *traj, *sc, *AB, *lam, *yh, *wact, *dtraj, *mus;
@@ -185,28 +195,40 @@ struct QuadCondensedModel {
         if (sc_out && lane < 3) { sc_out[2 * lane] = s; sc_out[2 * lane + 1] = c; }
         s6[0] = shfl(s, 0); s6[1] = shfl(c, 0); s6[2] = shfl(s, 1); s6[3] = shfl(c, 1); s6[4] = shfl(s, 2); s6[5] = shfl(c, 2);
     }
+    /// The four stages run as a rolled loop (same operations in the same order as the unrolled formula
+    /// x + h/6 (((k1 + 2 k2) + 2 k3) + k4): multiplying k4 by 1.0 is exact): a quarter of the code, and the rollout is the one
+    /// sweep whose straight-line body otherwise misses the instruction cache on every step (57 % of its stall samples were
+    /// `no_instruction` with 16 warps per SM in different functions, profiles/r02_c_quadc_ncu_regions.txt).
     __device__ __forceinline__ static void rk4_step(double *x, const double *uk, double *sc_out) {
         using namespace qc;
-        double s6[6], t[NX], k1[NX], k2[NX], k3[NX], k4[NX];
-        stage_sincos(x, s6, sc_out);
-        F::fc(x, uk, s6, k1);
+        double s6[6], t[NX], k[NX], acc[NX];
+#pragma unroll 1
+        for (int j = 0; j < 4; ++j) {
+            if (j == 0) {
 #pragma unroll
-        for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k1[i];
-        stage_sincos(t, s6, sc_out ? sc_out + 6 : nullptr);
-        F::fc(t, uk, s6, k2);
+                for (int i = 0; i < NX; ++i) t[i] = x[i];
+            } else {
+                const double c = j == 3 ? h : hh;
 #pragma unroll
-        for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k2[i];
-        stage_sincos(t, s6, sc_out ? sc_out + 12 : nullptr);
-        F::fc(t, uk, s6, k3);
+                for (int i = 0; i < NX; ++i) t[i] = x[i] + c * k[i];
+            }
+            stage_sincos(t, s6, sc_out ? sc_out + 6 * j : nullptr);
+            F::fc(t, uk, s6, k);
+            if (j == 0) {
 #pragma unroll
-        for (int i = 0; i < NX; ++i) t[i] = x[i] + h * k3[i];
-        stage_sincos(t, s6, sc_out ? sc_out + 18 : nullptr);
-        F::fc(t, uk, s6, k4);
+                for (int i = 0; i < NX; ++i) acc[i] = k[i];
+            } else {
+                const double w = j == 3 ? 1.0 : 2.0;
 #pragma unroll
-        for (int i = 0; i < NX; ++i) x[i] = x[i] + h6 * (((k1[i] + 2.0 * k2[i]) + 2.0 * k3[i]) + k4[i]);
+                for (int i = 0; i < NX; ++i) acc[i] = acc[i] + w * k[i];
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < NX; ++i) x[i] = x[i] + h6 * acc[i];
     }
     /// Rollout (ss.py:24): fills traj and sc.
     __device__ __noinline__ void rollout(const double *u) {
+        PANTR_QC_LOCALS;
         double x[NX], uk[NU], un[NU];
 #pragma unroll
         for (int i = 0; i < NX; ++i) { x[i] = x0[i]; traj[i] = x[i]; }
@@ -222,11 +244,12 @@ struct QuadCondensedModel {
         }
         double s6[6];
         stage_sincos(x, s6, sc + 24 * N);
-        rolled = u;
+        this->rolled = u;
         __syncwarp();
     }
     /// Cost (ss.py:32-36): lane = node, node k < N contributes l(x_k, u_k), node N contributes l_N(x_N).
     __device__ __forceinline__ double cost(const double *u) const {
+        PANTR_QC_LOCALS;
         using namespace qc;
         double p = 0;
         for (int k = lane_id(); k <= N; k += 32) {
@@ -248,6 +271,7 @@ struct QuadCondensedModel {
         return warp_sum(p);
     }
     __device__ __forceinline__ void constraints(double *g) const {
+        PANTR_QC_LOCALS;
         for (int k = lane_id(); k <= N; k += 32) {
             double x[NX], s6[6], c[NC];
             qc::ldv<NX>(traj + k * NX, x); qc::ldv<6>(sc + 24 * k, s6);
@@ -259,6 +283,7 @@ struct QuadCondensedModel {
     /// Augmented-Lagrangian terms (casadi_generator/__init__.py:64-72), lane = node: zeta = c + y / Sigma,
     /// z_hat = fmax(zl, fmin(zeta, zu)), d = zeta - z_hat, y_hat = Sigma d; returns 1/2 y_hat' d.
     __device__ __noinline__ double al_terms(const double *y, const double *S, double *yhat, double *wa) const {
+        PANTR_QC_LOCALS;
         double p = 0;
         for (int k = lane_id(); k <= N; k += 32) {
             double x[NX], s6[6], c[NC], a = 0;
@@ -312,6 +337,7 @@ struct QuadCondensedModel {
     /// Step Jacobians: lane = (step, column) task.  Step 0 gets all 13 columns, the other steps the columns
     /// that vary; the constant columns (FC_CONST_COLS: the same at every step) are then copied from step 0.
     __device__ __noinline__ void build_AB(const double *u) {
+        PANTR_QC_LOCALS;
         constexpr int NV = __builtin_popcount(VAR_COLS), NCST = NZ - NV;
         const int total = NZ + (N - 1) * NV;
         for (int t = lane_id(); t < total; t += 32) {
@@ -346,17 +372,20 @@ struct QuadCondensedModel {
     template <class Fin>
     __device__ __forceinline__ void adjoint_recurrence(double *rows, double *out, Fin fin) {
         using namespace qc;
+        const int N = this->N;
+        const double *const AB = this->AB;
         const StepRing R = step_ring();
+        const unsigned slot0 = smem_addr(R.slot), bar0 = smem_addr(R.bar);
         const int lane = lane_id();
         const int cl = lane < NZ ? lane : NZ - 1;
         auto refill = [&](int i) { // record of step i -> slot i % D: AB by lane 0 (TMA), the row by lanes 0..6 (cp.async)
             const int k = N - 1 - i, sl = i & (RING_D - 1);
-            double *dst = R.slot + sl * RING_SLOT;
+            const unsigned dst = slot0 + sl * (RING_SLOT * 8), bar = bar0 + sl * 8;
             if (lane == 0) {
-                mbar_expect_tx(R.bar + sl, ABS * 8);
-                bulk_g2s(dst, AB + size_t(k) * ABS, ABS * 8, R.bar + sl);
+                mbar_expect_tx_a(bar, ABS * 8);
+                bulk_g2s_a(dst, AB + size_t(k) * ABS, ABS * 8, bar);
             }
-            if (lane < ROW / 2) cp_async_16(dst + ABS + 2 * lane, rows + size_t(k) * ROW + 2 * lane);
+            if (lane < ROW / 2) cp_async_16_a(dst + ABS * 8 + 16 * lane, rows + size_t(k) * ROW + 2 * lane);
         };
         if (lane == 0) {
 #pragma unroll
@@ -376,7 +405,7 @@ struct QuadCondensedModel {
 #pragma unroll 1
         for (int i = 0; i < N; ++i) {
             const int k = N - 1 - i, sl = i & (RING_D - 1);
-            mbar_wait(R.bar + sl, (i / RING_D) & 1);
+            mbar_wait_a(bar0 + sl * 8, (i / RING_D) & 1);
             const double *rec = R.slot + sl * RING_SLOT;
             double col[NX], w[NX];
             ldv<NX>(rec + cl * COL, col);
@@ -405,6 +434,7 @@ struct QuadCondensedModel {
     };
     /// Gradient of  s f + yh' g  wrt u (s = cost_scale); leaves lambda_1..N in lam.
     __device__ __noinline__ void adjoint(const double *u, double cost_scale, double *grad) {
+        PANTR_QC_LOCALS;
         using namespace qc;
         for (int k = lane_id(); k <= N; k += 32) { // rows of the recurrence: node sources q_k = s dl/dx + J_c' yh_k, and u_k
             if (k < N) {
@@ -422,19 +452,23 @@ struct QuadCondensedModel {
             }
         }
         __syncwarp();
-        adjoint_recurrence(lam, grad, GradFin{cost_scale});
+        adjoint_recurrence(this->lam, grad, GradFin{cost_scale});
     }
     /// Tangent recurrence dx_{k+1} = AB_k (dx_k, v_k): lane r < 9 owns row r, one fma chain over the 13 columns;
     /// AB_k arrives through the ring, (dx_k, v_k) through the exchange buffer.
     __device__ __noinline__ void tangent(const double *v) {
         using namespace qc;
+        const int N = this->N;
+        const double *const AB = this->AB;
+        double *const dtraj = this->dtraj;
         const StepRing R = step_ring();
+        const unsigned slot0 = smem_addr(R.slot), bar0 = smem_addr(R.bar);
         const int lane = lane_id();
         const int rl = lane < NX ? lane : NX - 1;
         auto refill = [&](int k) { // lane 0 only
             const int sl = k & (RING_D - 1);
-            mbar_expect_tx(R.bar + sl, ABS * 8);
-            bulk_g2s(R.slot + sl * RING_SLOT, AB + size_t(k) * ABS, ABS * 8, R.bar + sl);
+            mbar_expect_tx_a(bar0 + sl * 8, ABS * 8);
+            bulk_g2s_a(slot0 + sl * (RING_SLOT * 8), AB + size_t(k) * ABS, ABS * 8, bar0 + sl * 8);
         };
         if (lane == 0) {
 #pragma unroll
@@ -451,7 +485,7 @@ struct QuadCondensedModel {
             const int sl = k & (RING_D - 1);
             double vn = 0;
             if (k + 1 < N && lane < NU) vn = v[NU * (k + 1) + lane];
-            mbar_wait(R.bar + sl, (k / RING_D) & 1);
+            mbar_wait_a(bar0 + sl * 8, (k / RING_D) & 1);
             const double *rec = R.slot + sl * RING_SLOT;
             double row[NZ], z[NZ];
 #pragma unroll
@@ -469,6 +503,7 @@ struct QuadCondensedModel {
     }
     /// node term of the second-order adjoint at node k: (s hess l + sum_i yh_i hess c_i + J_c' W J_c) dx_k
     __device__ __forceinline__ void node_second_order(int k, double cost_scale, double *out) const {
+        PANTR_QC_LOCALS;
         using namespace qc;
         double x[NX], s6[6], y4[NC], wa[NC], dx[NX], bx[NX], dc[NC], t[NC], ax[NX];
         ldv<NX>(traj + k * NX, x); ldv<6>(sc + 24 * k, s6); ldv<NC>(yh + NC * k, y4); ldv<NC>(wact + NC * k, wa);
@@ -485,6 +520,7 @@ struct QuadCondensedModel {
     /// row k of mus = [ d/dx_k[J_step' lambda_{k+1}] (dx_k, v_k) + node term of node k (k >= 1; row N = terminal node term) |
     ///                  d/du_k[...] (dx_k, v_k) + s 2 w_u v_k ].
     __device__ __noinline__ void second_order_sources(const double *u, const double *v, double cost_scale) {
+        PANTR_QC_LOCALS;
         using namespace qc;
         for (int k = lane_id(); k <= N; k += 32) {
             if (k == N) {

@@ -41,6 +41,28 @@ __device__ __forceinline__ void bulk_g2s(double *dst, const double *src, unsigne
                  "l"(src), "r"(bytes), "r"(smem_addr(bar))
                  : "memory");
 }
+__device__ __forceinline__ void mbar_expect_tx_a(unsigned bar_addr, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_a(unsigned dst_addr, const double *src, unsigned bytes, unsigned bar_addr) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_addr), "l"(src),
+                 "r"(bytes), "r"(bar_addr)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait_a(unsigned bar_addr, unsigned parity) {
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "WAIT_%=:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra DONE_%=;\n"
+                 "bra WAIT_%=;\n"
+                 "DONE_%=:\n"
+                 "}" ::"r"(bar_addr), "r"(parity)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_16_a(unsigned dst_addr, const double *g) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_addr), "l"(g) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
     asm volatile("{\n"
                  ".reg .pred p;\n"

@@ -46,7 +46,7 @@ if what in ("all", "parity"):
                 good &= check("plant", xn[b], ou.simulate(pid, x0[b], u[b, :4]))
             print(f"{name} N={N}: eval / face parity {'bit-exact' if good else 'FAILED'}", flush=True)
         for N, B in ((10, 6), (30, 3)):
-            solver, _ = pb.make_solver(pb.benchmark_options(name) + ["alm.max_time=10h"])  # the oracle has no clock
+            solver, _ = pb.make_solver(pb.benchmark_options(name) + ["alm.max_time=600min"])  # the oracle has no clock
             prob = pb.BatchedProblem(name, N)
             solver.set_exec_mode(prob, "warp")
             x0 = np.tile(prob.initial_state(), (B, 1)); x0[1:] += 0.03 * rng.standard_normal((B - 1, 9))

@@ -96,7 +96,7 @@ def test_full_solve_at_the_largest_horizon(pb):
     """One uncapped ALM+PANTR solve at N = 120 (the reference itself stops at N = 60, problems/CMakeLists.txt:33):
     device vs oracle, bit for bit, for the nominal initial state and a perturbed one."""
     name, pid, N = "realistic_quadcopter", 6, 120
-    solver, _ = pb.make_solver(pb.benchmark_options(name) + ["alm.max_time=10h"])
+    solver, _ = pb.make_solver(pb.benchmark_options(name) + ["alm.max_time=600min"])
     prob = pb.BatchedProblem(name, N)
     x0 = np.tile(prob.initial_state(), (2, 1)); x0[1] += 0.01 * np.random.default_rng(120).standard_normal(9)
     u = np.tile(prob.initial_guess(), (2, 1)); y = np.zeros((2, prob.m))

@@ -170,7 +170,7 @@ def test_quadcopter_plant_step_and_boxes(pb, name, pid):
 def test_quadcopter_solve_parity(pb, name, pid, N, B):
     # alm.max_time=30s of the option set is enforced on the device clock; the oracle has no clock, and the
     # full-scale perturbations take up to 5 * 10^4 iterations
-    solver, _ = pb.make_solver(pb.benchmark_options(name) + ["alm.max_time=10h"])
+    solver, _ = pb.make_solver(pb.benchmark_options(name) + ["alm.max_time=600min"])
     prob = pb.BatchedProblem(name, N)
     rng = np.random.default_rng(200 + 10 * pid + N)
     x0 = quad_states(B, rng)
@@ -207,7 +207,7 @@ def test_quadcopter_solve_parity(pb, name, pid, N, B):
 def test_quadcopter_thread_per_instance_path_matches_its_oracle(pb, name, pid, N, B):
     """ThreadExec (32 instances per warp, interleaved vectors, forward-over-adjoint sweeps) against the oracle's
     forward-over-adjoint formulation: same bits; against the condensed default path: same solution to rounding."""
-    solver, _ = pb.make_solver(pb.benchmark_options(name) + ["alm.max_time=10h"])
+    solver, _ = pb.make_solver(pb.benchmark_options(name) + ["alm.max_time=600min"])
     prob = pb.BatchedProblem(name, N)
     rng = np.random.default_rng(300 + 10 * pid + N)
     x0 = quad_states(B, rng) * 0.2 + 0.8 * prob.initial_state()
