@@ -26,12 +26,14 @@
 // formulation (agreement to rounding, tests/test_oracle_quadcopter.py).
 //
 // Per-instance model workspace (global memory):
-//   AB N x 130 (13 columns x (9 rows + pad): 1040 bytes per step) | lam, mus (N+1) x 14 rows
+//   ABv N x NV x 10: the columns of AB_k that vary from step to step (FC_CONST_COLS marks the others: 7 of 13 vary for
+//   both models, 560 bytes per step) | ABc 13 x 10: the constant columns, once per instance (the recurrences keep them
+//   in registers) | lam, mus (N+1) x 14 rows
 //   [x-part source -> adjoint state (9) | u-part addend (4) | pad] of the two adjoint recurrences |
 //   traj, dtraj (N+1) x 9 | sc (4N+1) x 6 sin/cos of every stage point | yh, wact 4(N+1)
 // The three recurrences are latency chains: every operand of a step must already sit in shared memory when the
 // step starts.  A step's record is therefore fetched PANTR_QC_RING_DEPTH steps ahead into a shared-memory ring:
-// AB_k (1040 bytes) by ONE elected lane with cp.async.bulk (TMA; SASS: UBLKCP) completing on a per-slot mbarrier the
+// the variable columns of AB_k (560 bytes) by ONE elected lane with cp.async.bulk (TMA; SASS: UBLKCP) completing on a per-slot mbarrier the
 // warp waits on; the 112-byte source row of the adjoint recurrences by cp.async (LDGSTS) of 7 lanes -- the rows are
 // written by the lanes just before the recurrence starts, and cp.async is a generic-proxy read ordered by
 // __syncwarp like any load, whereas a bulk copy of freshly written global data needs a gpu-scope fence first (AB gets
@@ -106,20 +108,21 @@ __device__ __forceinline__ void ldv(const double *p, double *out) {
 #endif
 namespace qc {
 constexpr int COL = 10;        // doubles per column of AB_k (9 + 1: columns start 16-byte aligned, LDS.128)
-constexpr int ABS = NZ * COL;  // doubles per step of AB (1040 bytes: bulk copies move multiples of 16 bytes)
+constexpr int ABC = NZ * COL;  // doubles of the constant-column block (one per instance)
 constexpr int ROW = 14;        // doubles per row of lam / mus (112 bytes)
-constexpr int RING_D = PANTR_QC_RING_DEPTH, RING_SLOT = ABS + ROW;
+constexpr int RING_D = PANTR_QC_RING_DEPTH;
 static_assert((RING_D & (RING_D - 1)) == 0 && RING_D >= 2, "ring depth: a power of two");
 struct StepRing {
-    double *slot;              // RING_D x RING_SLOT
+    double *slot;              // RING_D slots: [the step's variable columns of AB | source row]
     double *xch;               // 2 x 16: the recurrence's state / operand exchange (ping-pong)
     unsigned long long *bar;   // RING_D mbarriers
 };
 /// One shared-memory ring per block, shared by the three recurrences (they never overlap in time).
+template <int SLOT>
 __device__ __forceinline__ StepRing step_ring() {
-    __shared__ __align__(16) double storage[RING_D * RING_SLOT + 32];
+    __shared__ __align__(16) double storage[RING_D * SLOT + 32];
     __shared__ __align__(8) unsigned long long bars[RING_D];
-    return StepRing{storage, storage + RING_D * RING_SLOT, bars};
+    return StepRing{storage, storage + RING_D * SLOT, bars};
 }
 } // namespace qc
 
@@ -132,11 +135,14 @@ struct QuadCondensedModel {
     static constexpr int NX = qc::NX, NU = qc::NU, NC = qc::NC, NZ = qc::NZ;
     static constexpr int MIN_BLOCKS = PANTR_QC_MIN_BLOCKS;
     static constexpr unsigned VAR_COLS = ~F::CONST_COLS & 0x1fffu; // columns of AB that differ from step to step
+    static constexpr int NV = __builtin_popcount(VAR_COLS), NCST = NZ - NV;
+    static constexpr int ABS = NV * qc::COL;            // doubles per step of ABv (a multiple of 2: 16-byte bulk copies)
+    static constexpr int RING_SLOT = ABS + qc::ROW;     // doubles per ring slot
     static constexpr bool HAS_SCALE = true;
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int N) { return NC * (N + 1); }
     __host__ __device__ static int traj_doubles(int N) {
-        const int d = N * qc::ABS + 2 * (N + 1) * qc::ROW + 2 * (N + 1) * NX + (4 * N + 1) * 6 + 2 * NC * (N + 1);
+        const int d = N * ABS + qc::ABC + 2 * (N + 1) * qc::ROW + 2 * (N + 1) * NX + (4 * N + 1) * 6 + 2 * NC * (N + 1);
         return (d + 1) / 2 * 2; // the solver vectors behind it stay 16-byte aligned
     }
     __host__ __device__ static double C_lb(int i) { return (i & 3) == 0 ? 0.0 : -qc::dtilt_max; } // quadcopter.py:56-59, ss.py:28-29
@@ -161,11 +167,12 @@ struct QuadCondensedModel {
     const int N = this->N;                                                                                               \
     const double *const x0 = this->x0;                                                                                   \
     double *const traj = this->traj, *const sc = this->sc, *const AB = this->AB, *const lam = this->lam,                 \
-                  *const yh = this->yh, *const wact = this->wact, *const dtraj = this->dtraj, *const mus = this->mus;    \
-    (void)N; (void)x0; (void)traj; (void)sc; (void)AB; (void)lam; (void)yh; (void)wact; (void)dtraj; (void)mus
+                  *const yh = this->yh, *const wact = this->wact, *const dtraj = this->dtraj, *const mus = this->mus,    \
+                  *const ABc = this->ABc;                                                                                \
+    (void)N; (void)x0; (void)traj; (void)sc; (void)AB; (void)lam; (void)yh; (void)wact; (void)dtraj; (void)mus; (void)ABc
     int N;
     const double *x0;
-    double *traj, *sc, *AB, *lam, *yh, *wact, *dtraj, *mus;
+    double *traj, *sc, *AB, *ABc, *lam, *yh, *wact, *dtraj, *mus;
     bool hvp_ready;
     /// The vector whose rollout traj / sc currently hold.  PANTR evaluates psi(x_hat) and then, one step later,
     /// psi_grad_psi at a copy of the same point (pantr.tpp:303-316: prox.x = curr.x_hat): the solver moves the tag
@@ -180,7 +187,7 @@ struct QuadCondensedModel {
         N = N_; x0 = x0_; hvp_ready = false; rolled = nullptr;
         double *p = ws;
         // the bulk-copied arrays first: the block's workspace starts 128-byte aligned, AB steps are 944 bytes, rows 112
-        AB = p; p += N * qc::ABS; lam = p; p += (N + 1) * qc::ROW; mus = p; p += (N + 1) * qc::ROW;
+        AB = p; p += N * ABS; ABc = p; p += qc::ABC; lam = p; p += (N + 1) * qc::ROW; mus = p; p += (N + 1) * qc::ROW;
         traj = p; p += (N + 1) * NX; dtraj = p; p += (N + 1) * NX;
         sc = p; p += (4 * N + 1) * 6; yh = p; p += NC * (N + 1); wact = p;
     }
@@ -334,33 +341,25 @@ struct QuadCondensedModel {
         }
         return c;
     }
-    /// Step Jacobians: lane = (step, column) task.  Step 0 gets all 13 columns, the other steps the columns
-    /// that vary; the constant columns (FC_CONST_COLS: the same at every step) are then copied from step 0.
+    /// Step Jacobians: lane = (step, column) task.  Every step gets the columns that vary (ABv); the constant columns
+    /// (FC_CONST_COLS: the same at every step of every instance) are computed once, at step 0 (ABc).
     __device__ __noinline__ void build_AB(const double *u) {
         PANTR_QC_LOCALS;
-        constexpr int NV = __builtin_popcount(VAR_COLS), NCST = NZ - NV;
-        const int total = NZ + (N - 1) * NV;
+        const int total = N * NV + NCST;
         for (int t = lane_id(); t < total; t += 32) {
-            int k = 0, c = t;
-            if (t >= NZ) { const int q = t - NZ; k = 1 + q / NV; c = nth_col(VAR_COLS, q % NV); }
+            int k = 0, c;
+            double *col;
+            if (t < N * NV) { k = t / NV; const int j = t % NV; c = nth_col(VAR_COLS, j); col = AB + size_t(k) * ABS + j * qc::COL; }
+            else { c = nth_col(F::CONST_COLS, t - N * NV); col = ABc + c * qc::COL; }
             double xk[NX], uk[NU], s[24], e[NZ], out[NX];
             qc::ldv<NX>(traj + k * NX, xk); qc::ldv<NU>(u + NU * k, uk); qc::ldv<24>(sc + 24 * k, s);
 #pragma unroll
             for (int i = 0; i < NZ; ++i) e[i] = i == c ? 1.0 : 0.0;
             step_tangent(xk, uk, s, e, e + NX, out);
-            double *col = AB + size_t(k) * qc::ABS + c * qc::COL;
 #pragma unroll
             for (int i = 0; i < NX; ++i) col[i] = out[i];
         }
-        __syncwarp();
-        if (NCST > 0) {
-            const int ncopy = (N - 1) * NCST * NX;
-            for (int t = lane_id(); t < ncopy; t += 32) {
-                const int k = 1 + t / (NCST * NX), r = t % (NCST * NX), c = nth_col(F::CONST_COLS, r / NX), i = r % NX;
-                AB[size_t(k) * qc::ABS + c * qc::COL + i] = AB[c * qc::COL + i];
-            }
-        }
-        __threadfence(); // the recurrences read AB through the async proxy (TMA reads L2): the stores must have landed
+        __threadfence(); // the recurrences read ABv through the async proxy (TMA reads L2): the stores must have landed
         __syncwarp();
     }
     /// Adjoint recurrence w_k = AB_k' w_{k+1} + src_k over k = N-1..0 (lane c < 13 owns entry c of the product: one
@@ -374,11 +373,16 @@ struct QuadCondensedModel {
         using namespace qc;
         const int N = this->N;
         const double *const AB = this->AB;
-        const StepRing R = step_ring();
+        const StepRing R = step_ring<RING_SLOT>();
         const unsigned slot0 = smem_addr(R.slot), bar0 = smem_addr(R.bar);
         const int lane = lane_id();
         const int cl = lane < NZ ? lane : NZ - 1;
-        auto refill = [&](int i) { // record of step i -> slot i % D: AB by lane 0 (TMA), the row by lanes 0..6 (cp.async)
+        // this lane's column of AB_k: constant (kept in registers for the whole sweep) or the vj-th variable column
+        const bool is_var = (VAR_COLS >> cl) & 1u;
+        const int vj = is_var ? __popc(VAR_COLS & ((1u << cl) - 1u)) : 0;
+        double ccol[NX];
+        ldv<NX>(this->ABc + cl * COL, ccol);
+        auto refill = [&](int i) { // record of step i -> slot i % D: ABv_k by lane 0 (TMA), the row by lanes 0..6 (cp.async)
             const int k = N - 1 - i, sl = i & (RING_D - 1);
             const unsigned dst = slot0 + sl * (RING_SLOT * 8), bar = bar0 + sl * 8;
             if (lane == 0) {
@@ -408,7 +412,11 @@ struct QuadCondensedModel {
             mbar_wait_a(bar0 + sl * 8, (i / RING_D) & 1);
             const double *rec = R.slot + sl * RING_SLOT;
             double col[NX], w[NX];
-            ldv<NX>(rec + cl * COL, col);
+            if (is_var) ldv<NX>(rec + vj * COL, col);
+            else {
+#pragma unroll
+                for (int r = 0; r < NX; ++r) col[r] = ccol[r];
+            }
             const double addend = rec[ABS + cl];
             ldv<NX>(R.xch + 16 * cur, w);
             double a = col[0] * w[0];
@@ -461,10 +469,13 @@ struct QuadCondensedModel {
         const int N = this->N;
         const double *const AB = this->AB;
         double *const dtraj = this->dtraj;
-        const StepRing R = step_ring();
+        const StepRing R = step_ring<RING_SLOT>();
         const unsigned slot0 = smem_addr(R.slot), bar0 = smem_addr(R.bar);
         const int lane = lane_id();
         const int rl = lane < NX ? lane : NX - 1;
+        double crow[NZ]; // this lane's row of the constant columns (the entries of the variable columns stay unused)
+#pragma unroll
+        for (int c = 0; c < NZ; ++c) crow[c] = ((VAR_COLS >> c) & 1u) ? 0.0 : this->ABc[c * COL + rl];
         auto refill = [&](int k) { // lane 0 only
             const int sl = k & (RING_D - 1);
             mbar_expect_tx_a(bar0 + sl * 8, ABS * 8);
@@ -488,8 +499,14 @@ struct QuadCondensedModel {
             mbar_wait_a(bar0 + sl * 8, (k / RING_D) & 1);
             const double *rec = R.slot + sl * RING_SLOT;
             double row[NZ], z[NZ];
+            {
+                int j = 0; // compile-time after unrolling: index among the variable columns
 #pragma unroll
-            for (int c = 0; c < NZ; ++c) row[c] = rec[c * COL + rl];
+                for (int c = 0; c < NZ; ++c) {
+                    if ((VAR_COLS >> c) & 1u) { row[c] = rec[j * COL + rl]; ++j; }
+                    else row[c] = crow[c];
+                }
+            }
             ldv<NZ>(R.xch + 16 * cur, z);
             double a = row[0] * z[0];
 #pragma unroll
