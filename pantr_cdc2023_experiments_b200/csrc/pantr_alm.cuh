@@ -58,6 +58,10 @@
         }
         Vec error_1 = e1, error_2 = e2, S = Sig, S_old = Sig_old;
         double norm_e_1 = nan(""), norm_e_2 = nan("");
+        // alm.tpp:54-58: Sigma, Sigma_old, error_1, error_2 start as NaN (a backtrack before the second successful
+        // iteration compares against them: NaN compares false and keeps Sigma_old)
+        for (int i = E::first(); i < m; i += E::STEP) e1[i] = e2[i] = Sig[i] = Sig_old[i] = nan("");
+        E::sync();
         if (a.initial_penalty > 0) {
             for (int i = E::first(); i < m; i += E::STEP) S[i] = a.initial_penalty;
         } else { // alm-helpers.tpp:47-59

@@ -49,4 +49,34 @@ PANTR_HD void pantr_sincos(double x, double *s, double *c) {
     }
 }
 
+/// The same evaluation with every multiply-add written as an explicit fma (reduction, both Horner chains, the final
+/// combinations): 20 fewer FP64 instructions per call, and |error| <= 1 ulp of the exactly reduced argument's sin / cos.
+/// Used by the condensed quadcopter formulation (device and oracle mirror); bit-reproducible like pantr_sincos.
+PANTR_HD void pantr_sincos_fma(double x, double *s, double *c) {
+    const bool ok = fabs(x) < 1.6e6;
+    const double fn = rint(x * 6.36619772367581382433e-01);
+    const int q = ok ? (int)fn : 0;
+    double r = fma(-fn, 1.57079632673412561417e+00, x);
+    r = fma(-fn, 6.07710050630396597660e-11, r);
+    r = fma(-fn, 2.02226624871116645580e-21, r);
+    if (!ok) r = NAN;
+    const double z = r * r;
+    double ps = fma(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08);
+    ps = fma(z, ps, 2.75573137070700676789e-06);
+    ps = fma(z, ps, -1.98412698298579493134e-04);
+    ps = fma(z, ps, 8.33333333332248946124e-03);
+    ps = fma(z, ps, -1.66666666666666324348e-01);
+    double pc = fma(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09);
+    pc = fma(z, pc, -2.75573143513906633035e-07);
+    pc = fma(z, pc, 2.48015872894767294178e-05);
+    pc = fma(z, pc, -1.38888888888741095749e-03);
+    pc = fma(z, pc, 4.16666666666666019037e-02);
+    const double sr = fma(r * z, ps, r);
+    const double cr = fma(z * z, pc, fma(-0.5, z, 1.0));
+    const bool swap = q & 1;
+    const double sv = swap ? cr : sr, cv = swap ? sr : cr;
+    *s = (q & 2) ? -sv : sv;
+    *c = ((q + 1) & 2) ? -cv : cv;
+}
+
 } // namespace pantr

@@ -202,36 +202,27 @@ struct QuadCondensedModel {
         if (sc_out && lane < 3) { sc_out[2 * lane] = s; sc_out[2 * lane + 1] = c; }
         s6[0] = shfl(s, 0); s6[1] = shfl(c, 0); s6[2] = shfl(s, 1); s6[3] = shfl(c, 1); s6[4] = shfl(s, 2); s6[5] = shfl(c, 2);
     }
-    /// The four stages run as a rolled loop (same operations in the same order as the unrolled formula
-    /// x + h/6 (((k1 + 2 k2) + 2 k3) + k4): multiplying k4 by 1.0 is exact): a quarter of the code, and the rollout is the one
-    /// sweep whose straight-line body otherwise misses the instruction cache on every step (57 % of its stall samples were
-    /// `no_instruction` with 16 warps per SM in different functions, profiles/r02_c_quadc_ncu_regions.txt).
+    /// (A rolled stage loop -- a quarter of the code, to relieve the instruction cache -- executed 50 % MORE warp
+    /// instructions (k / acc arrays through local memory, loop control) and was slower: profiles/r02_d_quadc_ncu_*.)
     __device__ __forceinline__ static void rk4_step(double *x, const double *uk, double *sc_out) {
         using namespace qc;
-        double s6[6], t[NX], k[NX], acc[NX];
-#pragma unroll 1
-        for (int j = 0; j < 4; ++j) {
-            if (j == 0) {
+        double s6[6], t[NX], k1[NX], k2[NX], k3[NX], k4[NX];
+        stage_sincos(x, s6, sc_out);
+        F::fc(x, uk, s6, k1);
 #pragma unroll
-                for (int i = 0; i < NX; ++i) t[i] = x[i];
-            } else {
-                const double c = j == 3 ? h : hh;
+        for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k1[i];
+        stage_sincos(t, s6, sc_out ? sc_out + 6 : nullptr);
+        F::fc(t, uk, s6, k2);
 #pragma unroll
-                for (int i = 0; i < NX; ++i) t[i] = x[i] + c * k[i];
-            }
-            stage_sincos(t, s6, sc_out ? sc_out + 6 * j : nullptr);
-            F::fc(t, uk, s6, k);
-            if (j == 0) {
+        for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k2[i];
+        stage_sincos(t, s6, sc_out ? sc_out + 12 : nullptr);
+        F::fc(t, uk, s6, k3);
 #pragma unroll
-                for (int i = 0; i < NX; ++i) acc[i] = k[i];
-            } else {
-                const double w = j == 3 ? 1.0 : 2.0;
+        for (int i = 0; i < NX; ++i) t[i] = x[i] + h * k3[i];
+        stage_sincos(t, s6, sc_out ? sc_out + 18 : nullptr);
+        F::fc(t, uk, s6, k4);
 #pragma unroll
-                for (int i = 0; i < NX; ++i) acc[i] = acc[i] + w * k[i];
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < NX; ++i) x[i] = x[i] + h6 * acc[i];
+        for (int i = 0; i < NX; ++i) x[i] = x[i] + h6 * (((k1[i] + 2.0 * k2[i]) + 2.0 * k3[i]) + k4[i]);
     }
     /// Rollout (ss.py:24): fills traj and sc.
     __device__ __noinline__ void rollout(const double *u) {
