@@ -255,6 +255,22 @@ int pantr_b200_grid_size(const pantr_b200_solver *s);
 /* Measured FP64 FMA throughput of the device in TFLOP/s (independent DFMA chains, best of `reps`
  * launches): the denominator of the FP64 roofline bench.py reports. */
 int pantr_b200_measure_fp64_peak(int device, int reps, double *tflops);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * psi [B] and grad psi [B*n] of B instances, like pantr_b200_eval_psi_grad_psi_batch, but ALLOCATION-FREE: no solver
+ * handle, every buffer is a device pointer of the caller (x0 [B*nx], x [B*n], y and Sigma [B*m], NULL when m = 0), and
+ * the kernel's per-block model workspace is a static device array of PANTR_B200_NOALLOC_SCRATCH_BYTES inside the
+ * library (held by every GPU that loads it, until exit).  Calls cudaMalloc / cudaFree / no allocating routine.
+ * Runs on `stream` (a cudaStream_t; NULL = the default stream) of the CURRENT device and returns without
+ * synchronising.  Limits: 1 <= horizon <= PANTR_B200_NOALLOC_MAX_HORIZON, 0 <= B <= PANTR_B200_NOALLOC_MAX_BATCH,
+ * else PANTR_B200_OUT_OF_RANGE.  All calls on a device share the array: calls that overlap on the GPU race --
+ * serialise them (one stream).  The array keeps the previous call's contents; nothing in it needs clearing. */
+#define PANTR_B200_NOALLOC_SCRATCH_BYTES (16u << 20)
+#define PANTR_B200_NOALLOC_MAX_HORIZON 120
+#define PANTR_B200_NOALLOC_MAX_BATCH (1 << 22)
+int pantr_b200_eval_psi_grad_psi_noalloc_device(int problem_id, int horizon, int64_t B, const double *d_x0,
+                                                const double *d_x, const double *d_y, const double *d_Sigma,
+                                                double *d_psi, double *d_grad_psi, void *stream);
 const char *pantr_b200_last_error(void);
 
 #ifdef __cplusplus

@@ -75,6 +75,8 @@ SYMBOLS = [
     "pantr_b200_eval_grad_psi_batch", "pantr_b200_eval_psi_grad_psi_batch",
     "pantr_b200_eval_prox_grad_step_batch", "pantr_b200_eval_proj_diff_g_batch",
     "pantr_b200_eval_proj_multipliers_batch", "pantr_b200_eval_inactive_indices_res_lna_batch",
+    # allocation-free variant (no counterpart in the reference)
+    "pantr_b200_eval_psi_grad_psi_noalloc_device",
 ]
 
 _lib = None
@@ -137,6 +139,7 @@ def load():
     lib.pantr_b200_eval_proj_diff_g_batch.argtypes = [vp, i64, vp, vp]
     lib.pantr_b200_eval_proj_multipliers_batch.argtypes = [vp, i64, vp, f64]
     lib.pantr_b200_eval_inactive_indices_res_lna_batch.argtypes = [vp, i64, f64, vp, vp, vp, vp]
+    lib.pantr_b200_eval_psi_grad_psi_noalloc_device.argtypes = [C.c_int, C.c_int, i64, vp, vp, vp, vp, vp, vp, vp]
     _lib = lib
     return lib
 

@@ -8,6 +8,7 @@
 #include "problem_face.cuh"
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -196,3 +197,4 @@ __global__ void __launch_bounds__(256) fp64_peak_kernel(double *out, int iters, 
 
 #include "pantr_b200_host.inc"
 #include "pantr_b200_problem.inc"
+#include "pantr_b200_noalloc.inc"
