@@ -103,6 +103,10 @@ int oracle_eval_f_g(int problem_id, int N, const double *x0, const double *u, do
 void oracle_sincos(long n, const double *x, double *s, double *c) {
     for (long i = 0; i < n; ++i) pantr::pantr_sincos(x[i], s + i, c + i);
 }
+// the fma form the condensed quadcopter formulation uses (device: stage_sincos, oracle: quadcopter_condensed.hpp)
+void oracle_sincos_fma(long n, const double *x, double *s, double *c) {
+    for (long i = 0; i < n; ++i) pantr::pantr_sincos_fma(x[i], s + i, c + i);
+}
 
 // Evaluate psi, grad psi, yhat and (if v) hess_psi_prod at (u, y, Sigma) for initial state x0.
 int oracle_eval(int problem_id, int N, const double *x0, const double *u, const double *y,

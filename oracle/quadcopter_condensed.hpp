@@ -89,7 +89,7 @@ struct QuadcopterCondensed : Problem {
     }
 
     static void angles_sincos(const real_t *x, real_t *s6) {
-        for (int a = 0; a < 3; ++a) pantr::pantr_sincos(x[6 + a], &s6[2 * a], &s6[2 * a + 1]);
+        for (int a = 0; a < 3; ++a) pantr::pantr_sincos_fma(x[6 + a], &s6[2 * a], &s6[2 * a + 1]);
     }
 
     // ---- rollout (ss.py:24): states and the sin/cos of every RK4 stage point ----

@@ -50,27 +50,52 @@ PANTR_HD void pantr_sincos(double x, double *s, double *c) {
 }
 
 /// The same evaluation with every multiply-add written as an explicit fma (reduction, both Horner chains, the final
-/// combinations): 20 fewer FP64 instructions per call, and |error| <= 1 ulp of the exactly reduced argument's sin / cos.
-/// Used by the condensed quadcopter formulation (device and oracle mirror); bit-reproducible like pantr_sincos.
+/// combinations): half the dependent FP64 operations per call, and |error| <= 1 ulp of the exactly reduced argument's
+/// sin / cos.  Used by the condensed quadcopter formulation (device and oracle mirror); bit-reproducible like
+/// pantr_sincos.  On the device the 16 coefficients are read from constant memory (an FP64 instruction takes a constant
+/// bank operand for free, a literal costs two UMOV issue slots); the host reads the same literals.
+#define PANTR_SINCOS_COEFFS(X)                                                                                 \
+    X(0, 6.36619772367581382433e-01)   /* 2 / pi */                                                            \
+    X(1, 1.57079632673412561417e+00) X(2, 6.07710050630396597660e-11) X(3, 2.02226624871116645580e-21)         \
+    X(4, 1.58969099521155010221e-10) X(5, -2.50507602534068634195e-08) X(6, 2.75573137070700676789e-06)        \
+    X(7, -1.98412698298579493134e-04) X(8, 8.33333333332248946124e-03) X(9, -1.66666666666666324348e-01)       \
+    X(10, -1.13596475577881948265e-11) X(11, 2.08757232129817482790e-09) X(12, -2.75573143513906633035e-07)    \
+    X(13, 2.48015872894767294178e-05) X(14, -1.38888888888741095749e-03) X(15, 4.16666666666666019037e-02)
+#if defined(__CUDACC__)
+#define PANTR_SC_ENTRY(i, v) v,
+static __constant__ double pantr_sincos_k[16] = {PANTR_SINCOS_COEFFS(PANTR_SC_ENTRY)};
+#undef PANTR_SC_ENTRY
+#endif
+PANTR_HD double pantr_sincos_coeff(int i) {
+#if defined(__CUDA_ARCH__)
+    return pantr_sincos_k[i];
+#else
+#define PANTR_SC_CASE(k, v) case k: return v;
+    switch (i) { PANTR_SINCOS_COEFFS(PANTR_SC_CASE) default: return 0; }
+#undef PANTR_SC_CASE
+#endif
+}
 PANTR_HD void pantr_sincos_fma(double x, double *s, double *c) {
+#define K(i) pantr_sincos_coeff(i)
     const bool ok = fabs(x) < 1.6e6;
-    const double fn = rint(x * 6.36619772367581382433e-01);
+    const double fn = rint(x * K(0));
     const int q = ok ? (int)fn : 0;
-    double r = fma(-fn, 1.57079632673412561417e+00, x);
-    r = fma(-fn, 6.07710050630396597660e-11, r);
-    r = fma(-fn, 2.02226624871116645580e-21, r);
+    double r = fma(-fn, K(1), x);
+    r = fma(-fn, K(2), r);
+    r = fma(-fn, K(3), r);
     if (!ok) r = NAN;
     const double z = r * r;
-    double ps = fma(z, 1.58969099521155010221e-10, -2.50507602534068634195e-08);
-    ps = fma(z, ps, 2.75573137070700676789e-06);
-    ps = fma(z, ps, -1.98412698298579493134e-04);
-    ps = fma(z, ps, 8.33333333332248946124e-03);
-    ps = fma(z, ps, -1.66666666666666324348e-01);
-    double pc = fma(z, -1.13596475577881948265e-11, 2.08757232129817482790e-09);
-    pc = fma(z, pc, -2.75573143513906633035e-07);
-    pc = fma(z, pc, 2.48015872894767294178e-05);
-    pc = fma(z, pc, -1.38888888888741095749e-03);
-    pc = fma(z, pc, 4.16666666666666019037e-02);
+    double ps = fma(z, K(4), K(5));
+    ps = fma(z, ps, K(6));
+    ps = fma(z, ps, K(7));
+    ps = fma(z, ps, K(8));
+    ps = fma(z, ps, K(9));
+    double pc = fma(z, K(10), K(11));
+    pc = fma(z, pc, K(12));
+    pc = fma(z, pc, K(13));
+    pc = fma(z, pc, K(14));
+    pc = fma(z, pc, K(15));
+#undef K
     const double sr = fma(r * z, ps, r);
     const double cr = fma(z * z, pc, fma(-0.5, z, 1.0));
     const bool swap = q & 1;

@@ -193,33 +193,45 @@ struct QuadCondensedModel {
     }
 
     // ---- one RK4 step (quadcopter.py:49-55), executed by every lane; the sin/cos of the three angles of a
-    // stage point are computed by lanes 0..2 (one angle each) and broadcast.  sc_out: 4 x 6 or null. ----
-    __device__ __forceinline__ static void stage_sincos(const double *x, double *s6, double *sc_out) {
+    // stage point are computed by lanes 0..2 (one angle each, pantr_sincos_fma) and handed to the other lanes through
+    // shared memory: one 16-byte store, one __syncwarp and three 16-byte loads instead of twelve shuffles.  `buf`
+    // alternates 0 / 1 from stage to stage: the __syncwarp of the stage in between orders the reads of a buffer
+    // before its next writes.  sc_out: 4 x 6 or null. ----
+    __device__ __forceinline__ static void stage_sincos(const double *x, double *s6, double *sc_out, int buf) {
+        __shared__ __align__(16) double xs[2][8];
         const int lane = lane_id();
         const double ang = lane == 0 ? x[6] : (lane == 1 ? x[7] : x[8]);
         double s, c;
-        pantr_sincos(ang, &s, &c);
-        if (sc_out && lane < 3) { sc_out[2 * lane] = s; sc_out[2 * lane + 1] = c; }
-        s6[0] = shfl(s, 0); s6[1] = shfl(c, 0); s6[2] = shfl(s, 1); s6[3] = shfl(c, 1); s6[4] = shfl(s, 2); s6[5] = shfl(c, 2);
+        pantr_sincos_fma(ang, &s, &c);
+        if (lane < 3) {
+            *reinterpret_cast<double2 *>(&xs[buf][2 * lane]) = make_double2(s, c);
+            if (sc_out) { sc_out[2 * lane] = s; sc_out[2 * lane + 1] = c; }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const double2 v = *reinterpret_cast<const double2 *>(&xs[buf][2 * a]);
+            s6[2 * a] = v.x; s6[2 * a + 1] = v.y;
+        }
     }
     /// (A rolled stage loop -- a quarter of the code, to relieve the instruction cache -- executed 50 % MORE warp
     /// instructions (k / acc arrays through local memory, loop control) and was slower: profiles/r02_d_quadc_ncu_*.)
     __device__ __forceinline__ static void rk4_step(double *x, const double *uk, double *sc_out) {
         using namespace qc;
         double s6[6], t[NX], k1[NX], k2[NX], k3[NX], k4[NX];
-        stage_sincos(x, s6, sc_out);
+        stage_sincos(x, s6, sc_out, 0);
         F::fc(x, uk, s6, k1);
 #pragma unroll
         for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k1[i];
-        stage_sincos(t, s6, sc_out ? sc_out + 6 : nullptr);
+        stage_sincos(t, s6, sc_out ? sc_out + 6 : nullptr, 1);
         F::fc(t, uk, s6, k2);
 #pragma unroll
         for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k2[i];
-        stage_sincos(t, s6, sc_out ? sc_out + 12 : nullptr);
+        stage_sincos(t, s6, sc_out ? sc_out + 12 : nullptr, 0);
         F::fc(t, uk, s6, k3);
 #pragma unroll
         for (int i = 0; i < NX; ++i) t[i] = x[i] + h * k3[i];
-        stage_sincos(t, s6, sc_out ? sc_out + 18 : nullptr);
+        stage_sincos(t, s6, sc_out ? sc_out + 18 : nullptr, 1);
         F::fc(t, uk, s6, k4);
 #pragma unroll
         for (int i = 0; i < NX; ++i) x[i] = x[i] + h6 * (((k1[i] + 2.0 * k2[i]) + 2.0 * k3[i]) + k4[i]);
@@ -241,7 +253,7 @@ struct QuadCondensedModel {
             for (int i = 0; i < NX; ++i) traj[(k + 1) * NX + i] = x[i];
         }
         double s6[6];
-        stage_sincos(x, s6, sc + 24 * N);
+        stage_sincos(x, s6, sc + 24 * N, 0);
         this->rolled = u;
         __syncwarp();
     }

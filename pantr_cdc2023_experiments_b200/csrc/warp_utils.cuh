@@ -75,6 +75,27 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
                  : "memory");
 }
 
+// ---- shared-memory accesses by 32-bit shared-window address (the recurrences keep running addresses in registers;
+// through generic pointers the compiler rebuilt the window base -- S2R SR_CgaCtaId + LEA -- in every step) ----
+__device__ __forceinline__ double lds_f64(unsigned a) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ double2 lds_v2f64(unsigned a) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_f64(unsigned a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory"); }
+/// COUNT consecutive doubles from a 16-byte aligned shared address
+template <int COUNT>
+__device__ __forceinline__ void lds_vec(unsigned a, double *out) {
+#pragma unroll
+    for (int i = 0; i + 1 < COUNT; i += 2) { const double2 v = lds_v2f64(a + 8 * i); out[i] = v.x; out[i + 1] = v.y; }
+    if (COUNT & 1) out[COUNT - 1] = lds_f64(a + 8 * (COUNT - 1));
+}
+
 // ---- per-thread asynchronous copies (cp.async / LDGSTS: generic proxy, L2 -> shared) ----
 __device__ __forceinline__ void cp_async_16(double *smem, const double *g) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem)), "l"(g) : "memory");

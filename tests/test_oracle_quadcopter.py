@@ -103,18 +103,21 @@ def random_point(rng, N, spread=1.0):
     return x0, u, y, S
 
 
-def test_sincos_restatement():
-    """csrc/pantr_hd.h pantr_sincos vs libm over the angle ranges the models see."""
+@pytest.mark.parametrize("fn", ["oracle_sincos", "oracle_sincos_fma"])
+def test_sincos_restatement(fn):
+    """csrc/pantr_hd.h pantr_sincos (forward-over-adjoint formulation) and pantr_sincos_fma (condensed formulation)
+    vs libm over the angle ranges the models see."""
     lib = ou.load()
+    sincos = getattr(lib, fn)
     rng = np.random.default_rng(0)
     x = np.concatenate([rng.uniform(-4, 4, 20000), rng.uniform(-1000, 1000, 5000), [0.0, np.pi / 2, -np.pi, 1e-300]])
     s, c = np.zeros_like(x), np.zeros_like(x)
-    lib.oracle_sincos(C.c_long(x.size), ou.P(x), ou.P(s), ou.P(c))
+    sincos(C.c_long(x.size), ou.P(x), ou.P(s), ou.P(c))
     assert np.abs(s - np.sin(x)).max() <= 4e-16
     assert np.abs(c - np.cos(x)).max() <= 4e-16
     bad = np.array([np.inf, np.nan, 1e9])
     sb, cb = np.zeros(3), np.zeros(3)
-    lib.oracle_sincos(C.c_long(3), ou.P(bad), ou.P(sb), ou.P(cb))
+    sincos(C.c_long(3), ou.P(bad), ou.P(sb), ou.P(cb))
     assert np.isnan(sb).all() and np.isnan(cb).all()
 
 
@@ -187,10 +190,11 @@ def test_condensed_formulation_agrees_with_forward_over_adjoint(pid, N):
     pa, ga, ya, Ha = ou.eval_(pid, N, x0, u, y=y, Sigma=S, v=v, want_yhat=True)
     pc, gc, yc, Hc = ou.eval_(pid + 4, N, x0, u, y=y, Sigma=S, v=v, want_yhat=True)
     assert abs(pa - pc) <= 1e-14 * abs(pa)
-    np.testing.assert_array_equal(ya, yc)
+    # (the two formulations use the two sin/cos restatements: <= 1 ulp apart, not bit-equal)
+    np.testing.assert_allclose(yc, ya, rtol=0, atol=2e-14 * np.abs(ya).max())
     np.testing.assert_allclose(gc, ga, rtol=0, atol=2e-14 * np.abs(ga).max())
     np.testing.assert_allclose(Hc, Ha, rtol=0, atol=2e-14 * np.abs(Ha).max())
-    np.testing.assert_array_equal(ou.simulate(pid + 4, x0, u[:4]), ou.simulate(pid, x0, u[:4]))
+    np.testing.assert_allclose(ou.simulate(pid + 4, x0, u[:4]), ou.simulate(pid, x0, u[:4]), rtol=0, atol=1e-15)
 
 
 @pytest.mark.parametrize("pid", [5, 6])
