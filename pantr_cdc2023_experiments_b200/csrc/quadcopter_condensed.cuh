@@ -115,14 +115,15 @@ static_assert((RING_D & (RING_D - 1)) == 0 && RING_D >= 2, "ring depth: a power 
 struct StepRing {
     double *slot;              // RING_D slots: [the step's variable columns of AB | source row]
     double *xch;               // 2 x 16: the recurrence's state / operand exchange (ping-pong)
+    double *cst;               // the constant columns of AB (adjoint recurrences: one column per lane)
     unsigned long long *bar;   // RING_D mbarriers
 };
 /// One shared-memory ring per block, shared by the three recurrences (they never overlap in time).
-template <int SLOT>
+template <int SLOT, int CST>
 __device__ __forceinline__ StepRing step_ring() {
-    __shared__ __align__(16) double storage[RING_D * SLOT + 32];
+    __shared__ __align__(16) double storage[RING_D * SLOT + 32 + CST];
     __shared__ __align__(8) unsigned long long bars[RING_D];
-    return StepRing{storage, storage + RING_D * SLOT, bars};
+    return StepRing{storage, storage + RING_D * SLOT, storage + RING_D * SLOT + 32, bars};
 }
 } // namespace qc
 
@@ -353,7 +354,7 @@ struct QuadCondensedModel {
             int k = 0, c;
             double *col;
             if (t < N * NV) { k = t / NV; const int j = t % NV; c = nth_col(VAR_COLS, j); col = AB + size_t(k) * ABS + j * qc::COL; }
-            else { c = nth_col(F::CONST_COLS, t - N * NV); col = ABc + c * qc::COL; }
+            else { c = nth_col(F::CONST_COLS, t - N * NV); col = ABc + (t - N * NV) * qc::COL; } // ABc: the constant columns, compacted
             double xk[NX], uk[NU], s[24], e[NZ], out[NX];
             qc::ldv<NX>(traj + k * NX, xk); qc::ldv<NU>(u + NU * k, uk); qc::ldv<24>(sc + 24 * k, s);
 #pragma unroll
@@ -369,30 +370,35 @@ struct QuadCondensedModel {
     /// fma chain over the 9 rows; the 9 adjoint entries travel through shared memory).
     /// rows: [(N+1) x ROW]; row N = terminal value (in); row k < N holds the x-part source (entries 0..8) and the
     /// u-part addend (9..12) on entry, the adjoint state lambda_k in 0..8 on exit (row 0 keeps its source: x_0 does
-    /// not depend on u).  The u-part of step k, combined with its addend by `fin`, goes to out[4k + j].
-    /// Step i (k = N-1-i) reads its record -- AB_k and row k -- from ring slot i % D, filled D steps earlier.
-    template <class Fin>
-    __device__ __forceinline__ void adjoint_recurrence(double *rows, double *out, Fin fin) {
+    /// not depend on u).  The u-part of step k goes to out[4k + j]: product + addend (second-order adjoint), or, with
+    /// `grad`, fma(cs 2 w_u, addend, product) where the addend is u_kj (gradient).  Both are val = fma(coef, addend,
+    /// product) with a per-lane coef (fma(1, b, a) is a + b exactly), so the x- and u-lanes share one code path.
+    /// Step i (k = N-1-i) reads its record -- AB_k and row k -- from ring slot i % D, filled D steps earlier; slot,
+    /// barrier, parity and exchange-buffer addresses are running registers (32-bit shared-window addresses).
+    __device__ __noinline__ void adjoint_recurrence(double *rows, double *out, bool grad, double cs) {
         using namespace qc;
         const int N = this->N;
         const double *const AB = this->AB;
-        const StepRing R = step_ring<RING_SLOT>();
-        const unsigned slot0 = smem_addr(R.slot), bar0 = smem_addr(R.bar);
+        const StepRing R = step_ring<RING_SLOT, NCST * COL>();
+        const unsigned slot0 = smem_addr(R.slot), bar0 = smem_addr(R.bar), xch0 = smem_addr(R.xch);
+        constexpr unsigned SLOT_B = RING_SLOT * 8, RING_B = RING_D * SLOT_B;
         const int lane = lane_id();
         const int cl = lane < NZ ? lane : NZ - 1;
-        // this lane's column of AB_k: constant (kept in registers for the whole sweep) or the vj-th variable column
+        // this lane's column of AB_k: the vj-th variable column of the step's record, or a constant column (shared memory,
+        // loaded once per sweep)
         const bool is_var = (VAR_COLS >> cl) & 1u;
-        const int vj = is_var ? __popc(VAR_COLS & ((1u << cl) - 1u)) : 0;
-        double ccol[NX];
-        ldv<NX>(this->ABc + cl * COL, ccol);
-        auto refill = [&](int i) { // record of step i -> slot i % D: ABv_k by lane 0 (TMA), the row by lanes 0..6 (cp.async)
-            const int k = N - 1 - i, sl = i & (RING_D - 1);
-            const unsigned dst = slot0 + sl * (RING_SLOT * 8), bar = bar0 + sl * 8;
+        const int vj = __popc(VAR_COLS & ((1u << cl) - 1u));
+        const unsigned voff = is_var ? vj * (COL * 8) : 0u;
+        const unsigned caddr = smem_addr(R.cst) + (cl - vj) * (COL * 8);
+        const double coef = (grad && lane >= NX && lane < NZ) ? cs * (2 * wu(lane - NX)) : 1.0;
+        double *dst = lane < NX ? rows + size_t(N - 1) * ROW + lane : out + size_t(N - 1) * NU + (cl - NX);
+        const int dstride = lane < NX ? -ROW : -NU;
+        auto refill = [&](int k, unsigned rec, unsigned bar) { // record of step k: ABv_k by lane 0 (TMA), the row by lanes 0..6 (cp.async)
             if (lane == 0) {
                 mbar_expect_tx_a(bar, ABS * 8);
-                bulk_g2s_a(dst, AB + size_t(k) * ABS, ABS * 8, bar);
+                bulk_g2s_a(rec, AB + size_t(k) * ABS, ABS * 8, bar);
             }
-            if (lane < ROW / 2) cp_async_16_a(dst + ABS * 8 + 16 * lane, rows + size_t(k) * ROW + 2 * lane);
+            if (lane < ROW / 2) cp_async_16_a(rec + ABS * 8 + 16 * lane, rows + size_t(k) * ROW + 2 * lane);
         };
         if (lane == 0) {
 #pragma unroll
@@ -400,49 +406,41 @@ struct QuadCondensedModel {
             mbar_init_fence();
         }
         if (lane < NX) R.xch[lane] = rows[N * ROW + lane];
+        for (int t = lane; t < NCST * COL; t += 32) R.cst[t] = this->ABc[t];
         __syncwarp(); // the rows the lanes have just written are ordered before the copies below
 #pragma unroll
         for (int i = 0; i < RING_D; ++i) {
-            if (i < N) refill(i);
+            if (i < N) refill(N - 1 - i, slot0 + i * SLOT_B, bar0 + i * 8);
             cp_async_commit_group();
         }
         cp_async_wait_group<RING_D - 1>(); // step 0's row has landed ...
         __syncwarp();                      // ... in every lane's view
-        int cur = 0;
+        unsigned rec = slot0, bar = bar0, par = 0, xr = xch0, xw = xch0 + 128;
 #pragma unroll 1
         for (int i = 0; i < N; ++i) {
-            const int k = N - 1 - i, sl = i & (RING_D - 1);
-            mbar_wait_a(bar0 + sl * 8, (i / RING_D) & 1);
-            const double *rec = R.slot + sl * RING_SLOT;
+            mbar_wait_a(bar, par);
             double col[NX], w[NX];
-            if (is_var) ldv<NX>(rec + vj * COL, col);
-            else {
-#pragma unroll
-                for (int r = 0; r < NX; ++r) col[r] = ccol[r];
-            }
-            const double addend = rec[ABS + cl];
-            ldv<NX>(R.xch + 16 * cur, w);
+            lds_vec<NX>(is_var ? rec + voff : caddr, col);
+            const double addend = lds_f64(rec + ABS * 8 + 8 * cl);
+            lds_vec<NX>(xr, w);
             double a = col[0] * w[0];
 #pragma unroll
             for (int r = 1; r < NX; ++r) a = fma(col[r], w[r], a);
-            if (lane < NX) {
-                if (k > 0) { const double l = a + addend; rows[k * ROW + lane] = l; R.xch[16 * (cur ^ 1) + lane] = l; }
-            } else if (lane < NZ) out[NU * k + lane - NX] = fin(lane - NX, a, addend);
+            const double val = fma(coef, addend, a);
+            if (lane < NX ? i + 1 < N : lane < NZ) *dst = val;
+            dst += dstride;
+            if (lane < NX) sts_f64(xw + 8 * lane, val);
             cp_async_wait_group<RING_D - 2>(); // the next step's row has landed
-            __syncwarp();                      // slot `sl` has been read by every lane: refill it
-            if (i + RING_D < N) refill(i + RING_D);
+            __syncwarp();                      // slot `rec` has been read by every lane: refill it
+            const int kn = N - 1 - RING_D - i;
+            if (kn >= 0) refill(kn, rec, bar);
             cp_async_commit_group();
-            cur ^= 1;
+            { const unsigned t = xr; xr = xw; xw = t; }
+            rec += SLOT_B; bar += 8;
+            if (rec == slot0 + RING_B) { rec = slot0; bar = bar0; par ^= 1u; }
         }
         cp_async_wait_group<0>();
     }
-    struct GradFin { // u-part of the gradient: fma(s * 2 w_u, u_kj, AB' lambda)
-        double cs;
-        __device__ __forceinline__ double operator()(int j, double a, double ukj) const { return fma(cs * (2 * qc::wu(j)), ukj, a); }
-    };
-    struct SrcFin { // u-part of the Hessian-vector product: AB' mu + source
-        __device__ __forceinline__ double operator()(int, double a, double s) const { return a + s; }
-    };
     /// Gradient of  s f + yh' g  wrt u (s = cost_scale); leaves lambda_1..N in lam.
     __device__ __noinline__ void adjoint(const double *u, double cost_scale, double *grad) {
         PANTR_QC_LOCALS;
@@ -463,7 +461,7 @@ struct QuadCondensedModel {
             }
         }
         __syncwarp();
-        adjoint_recurrence(this->lam, grad, GradFin{cost_scale});
+        adjoint_recurrence(this->lam, grad, true, cost_scale);
     }
     /// Tangent recurrence dx_{k+1} = AB_k (dx_k, v_k): lane r < 9 owns row r, one fma chain over the 13 columns;
     /// AB_k arrives through the ring, (dx_k, v_k) through the exchange buffer.
@@ -471,54 +469,65 @@ struct QuadCondensedModel {
         using namespace qc;
         const int N = this->N;
         const double *const AB = this->AB;
-        double *const dtraj = this->dtraj;
-        const StepRing R = step_ring<RING_SLOT>();
-        const unsigned slot0 = smem_addr(R.slot), bar0 = smem_addr(R.bar);
+        const StepRing R = step_ring<RING_SLOT, NCST * COL>();
+        const unsigned slot0 = smem_addr(R.slot), bar0 = smem_addr(R.bar), xch0 = smem_addr(R.xch);
+        constexpr unsigned SLOT_B = RING_SLOT * 8, RING_B = RING_D * SLOT_B;
         const int lane = lane_id();
         const int rl = lane < NX ? lane : NX - 1;
         double crow[NZ]; // this lane's row of the constant columns (the entries of the variable columns stay unused)
+        {
+            int jc = 0; // compile-time after unrolling: index among the constant columns (ABc is compacted)
 #pragma unroll
-        for (int c = 0; c < NZ; ++c) crow[c] = ((VAR_COLS >> c) & 1u) ? 0.0 : this->ABc[c * COL + rl];
-        auto refill = [&](int k) { // lane 0 only
-            const int sl = k & (RING_D - 1);
-            mbar_expect_tx_a(bar0 + sl * 8, ABS * 8);
-            bulk_g2s_a(slot0 + sl * (RING_SLOT * 8), AB + size_t(k) * ABS, ABS * 8, bar0 + sl * 8);
-        };
+            for (int c = 0; c < NZ; ++c) {
+                if ((VAR_COLS >> c) & 1u) crow[c] = 0.0;
+                else { crow[c] = this->ABc[jc * COL + rl]; ++jc; }
+            }
+        }
         if (lane == 0) {
 #pragma unroll
             for (int sl = 0; sl < RING_D; ++sl) mbar_init(R.bar + sl, 1);
             mbar_init_fence();
-            for (int k = 0; k < RING_D && k < N; ++k) refill(k);
+            for (int k = 0; k < RING_D && k < N; ++k) {
+                mbar_expect_tx_a(bar0 + k * 8, ABS * 8);
+                bulk_g2s_a(slot0 + k * SLOT_B, AB + size_t(k) * ABS, ABS * 8, bar0 + k * 8);
+            }
         }
-        if (lane < NX) { R.xch[lane] = 0.0; dtraj[lane] = 0.0; }
+        double *dt = this->dtraj + lane; // lanes 0..8
+        if (lane < NX) { R.xch[lane] = 0.0; *dt = 0.0; }
         if (lane < NU) R.xch[NX + lane] = v[lane];
         __syncwarp();
-        int cur = 0;
+        const double *vnext = v + NU + (lane < NU ? lane : 0);
+        unsigned rec = slot0, bar = bar0, par = 0, xr = xch0, xw = xch0 + 128;
 #pragma unroll 1
         for (int k = 0; k < N; ++k) {
-            const int sl = k & (RING_D - 1);
             double vn = 0;
-            if (k + 1 < N && lane < NU) vn = v[NU * (k + 1) + lane];
-            mbar_wait_a(bar0 + sl * 8, (k / RING_D) & 1);
-            const double *rec = R.slot + sl * RING_SLOT;
+            if (k + 1 < N && lane < NU) vn = *vnext;
+            vnext += NU;
+            mbar_wait_a(bar, par);
             double row[NZ], z[NZ];
             {
                 int j = 0; // compile-time after unrolling: index among the variable columns
 #pragma unroll
                 for (int c = 0; c < NZ; ++c) {
-                    if ((VAR_COLS >> c) & 1u) { row[c] = rec[j * COL + rl]; ++j; }
+                    if ((VAR_COLS >> c) & 1u) { row[c] = lds_f64(rec + (j * COL + rl) * 8); ++j; }
                     else row[c] = crow[c];
                 }
             }
-            ldv<NZ>(R.xch + 16 * cur, z);
+            lds_vec<NZ>(xr, z);
             double a = row[0] * z[0];
 #pragma unroll
             for (int c = 1; c < NZ; ++c) a = fma(row[c], z[c], a);
-            if (lane < NX) { dtraj[(k + 1) * NX + lane] = a; R.xch[16 * (cur ^ 1) + lane] = a; }
-            if (lane < NU) R.xch[16 * (cur ^ 1) + NX + lane] = vn;
-            __syncwarp(); // slot `sl` has been read by every lane: refill it
-            if (lane == 0 && k + RING_D < N) refill(k + RING_D);
-            cur ^= 1;
+            dt += NX;
+            if (lane < NX) { *dt = a; sts_f64(xw + 8 * lane, a); }
+            if (lane < NU) sts_f64(xw + 8 * (NX + lane), vn);
+            __syncwarp(); // slot `rec` has been read by every lane: refill it
+            if (lane == 0 && k + RING_D < N) {
+                mbar_expect_tx_a(bar, ABS * 8);
+                bulk_g2s_a(rec, AB + size_t(k + RING_D) * ABS, ABS * 8, bar);
+            }
+            { const unsigned t = xr; xr = xw; xw = t; }
+            rec += SLOT_B; bar += 8;
+            if (rec == slot0 + RING_B) { rec = slot0; bar = bar0; par ^= 1u; }
         }
     }
     /// node term of the second-order adjoint at node k: (s hess l + sum_i yh_i hess c_i + J_c' W J_c) dx_k
@@ -613,7 +622,7 @@ struct QuadCondensedModel {
         }
         __syncwarp();
     }
-    __device__ __noinline__ void mu_recurrence(double *Hv) { adjoint_recurrence(mus, Hv, SrcFin{}); }
+    __device__ __forceinline__ void mu_recurrence(double *Hv) { adjoint_recurrence(this->mus, Hv, false, 0.0); }
     /// Hv = hess(s f + AL terms)(u) v; needs the caches of the last gradient at u (AB, lam, yh, wact, sc, traj).
     __device__ __forceinline__ void hvp(const double *u, const double *v, double cost_scale, double *Hv) {
         tangent(v);
