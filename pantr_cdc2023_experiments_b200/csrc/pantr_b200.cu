@@ -8,6 +8,7 @@
 #include "problem_face.cuh"
 #include <cstdio>
 #include <cstring>
+#include <new>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -44,6 +45,18 @@ template <class Model>
 __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __grid_constant__ SolverParams P,
                                                    const __grid_constant__ KernelArgs A) {
     __shared__ IterScalars it[3];
+    // The model and solver objects live in SHARED memory where the model asks for it (OBJECTS_IN_SHARED).  As locals they are address-taken (their routines are
+    // __noinline__ members), i.e. in local memory, one private copy per lane: ~0.5 KB x 32 lanes = 16 KB of L1 footprint
+    // per warp, re-read with LDL after every call and regularly evicted by the streamed workspace (the solver routines
+    // held ~20 % of the stall samples with ~5 % of the instructions, profiles/r02_e_quadc_ncu_*).  All scalars are
+    // warp-uniform, every lane writes the same values; read-modify-writes happen while the warp is converged.
+    // (Measured, profiles/r02_j_*: quadcopters +1.5 %, hanging chain -1.9 % -- its 12 warps per SM keep their copies
+    // in L1 and a generic load from shared memory is no faster than an LDL hit -- hence the per-model switch.)
+    constexpr size_t MDL_BYTES = (sizeof(Model) + 15) / 16 * 16, OBJ_BYTES = MDL_BYTES + sizeof(Pantr<Model>);
+    constexpr bool SH = Model::OBJECTS_IN_SHARED;
+    __shared__ __align__(16) unsigned char obj_shared[SH ? OBJ_BYTES : 16];
+    alignas(16) unsigned char obj_local[SH ? 16 : OBJ_BYTES];
+    unsigned char *const obj_mem = SH ? obj_shared : obj_local;
     extern __shared__ __align__(16) double dyn_smem[];
     double *ws = A.ws + size_t(blockIdx.x) * A.ws_stride;
     for (;;) {
@@ -58,20 +71,24 @@ __global__ void __launch_bounds__(32, Model::MIN_BLOCKS) solve_kernel(const __gr
         }
         long long t0 = clock64();
         const unsigned long long g0 = globaltimer_ns();
-        Model mdl;
+        __syncwarp();
+        Model &mdl = *new (obj_mem) Model;
         mdl.init(A.N, A.x0 + b * A.nx, ws);
-        Pantr<Model> S(mdl, P, it, A.n, A.m, ws + Model::traj_doubles(A.N), dyn_smem, A.smem_set);
+        Pantr<Model> &S = *new (obj_mem + MDL_BYTES) Pantr<Model>(mdl, P, it, A.n, A.m, ws + Model::traj_doubles(A.N), dyn_smem, A.smem_set);
         memset(&S.st, 0, sizeof(S.st));
         S.x = A.u + b * A.n;
-        for (int i = lane_id(); i < A.m; i += 32) S.y[i] = A.y[b * A.m + i];
         S.tracing = A.trace.rows != nullptr && (long long)b == A.trace.instance;
         S.tr = A.trace;
+        __syncwarp();
+        for (int i = lane_id(); i < A.m; i += 32) S.y[i] = A.y[b * A.m + i];
         __syncwarp();
         S.alm_solve();
         __syncwarp();
         for (int i = lane_id(); i < A.m; i += 32) A.y[b * A.m + i] = S.y[i];
+        __syncwarp();
         S.st.cycles = (unsigned long long)(clock64() - t0);
         S.st.elapsed_us = (unsigned)((globaltimer_ns() - g0) / 1000);
+        __syncwarp();
         if (lane_id() == 0) A.stats[b] = S.st;
         __syncwarp();
     }

@@ -128,6 +128,8 @@ struct Pantr {
     }
 #include "pantr_direction.cuh"
 #include "pantr_inner.cuh"
+    InnerState ist_;
+    InnerResult ires_;
 };
 
 } // namespace pantr

@@ -261,11 +261,11 @@
         return false;
     }
 
+    /// The loop state lives in the solver object (ist_, ires_), i.e. in shared memory for the warp kernel: as locals
+    /// passed by reference to the __noinline__ steps they were per-lane local-memory copies.
     __device__ InnerResult inner_solve(double tolerance_opt, bool always_overwrite, Vec errz, bool has_errz) {
-        InnerState s;
-        InnerResult res;
-        if (!inner_begin(s, res, tolerance_opt, always_overwrite, has_errz)) return res;
-        while (!inner_iterate(s, res, errz)) {}
-        return res;
+        if (!inner_begin(ist_, ires_, tolerance_opt, always_overwrite, has_errz)) return ires_;
+        while (!inner_iterate(ist_, ires_, errz)) {}
+        return ires_;
     }
 #include "pantr_alm.cuh"

@@ -140,6 +140,7 @@ struct QuadCondensedModel {
     static constexpr int ABS = NV * qc::COL;            // doubles per step of ABv (a multiple of 2: 16-byte bulk copies)
     static constexpr int RING_SLOT = ABS + qc::ROW;     // doubles per ring slot
     static constexpr bool HAS_SCALE = true;
+    static constexpr bool OBJECTS_IN_SHARED = true; // solve kernel: model / solver objects in shared memory (pantr_b200.cu)
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int N) { return NC * (N + 1); }
     __host__ __device__ static int traj_doubles(int N) {
