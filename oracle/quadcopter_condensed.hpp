@@ -95,23 +95,20 @@ struct QuadcopterCondensed : Problem {
     // ---- rollout (ss.py:24): states and the sin/cos of every RK4 stage point ----
     void rollout(const real_t *u) const {
         using namespace qcd;
-        real_t x[NX], t[NX], k1[NX], k2[NX], k3[NX], k4[NX];
+        real_t x[NX], t[NX], S[NX], kk[NX];
         for (int i = 0; i < NX; ++i) traj[i] = x[i] = x0[i];
         for (int k = 0; k < N; ++k) {
             const real_t *uk = u + NU * k;
             real_t *s = &sc[24 * k];
-            angles_sincos(x, s);
-            F::fc(x, uk, s, k1);
-            for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k1[i];
-            angles_sincos(t, s + 6);
-            F::fc(t, uk, s + 6, k2);
-            for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k2[i];
-            angles_sincos(t, s + 12);
-            F::fc(t, uk, s + 12, k3);
-            for (int i = 0; i < NX; ++i) t[i] = x[i] + h * k3[i];
-            angles_sincos(t, s + 18);
-            F::fc(t, uk, s + 18, k4);
-            for (int i = 0; i < NX; ++i) traj[(k + 1) * NX + i] = x[i] = x[i] + h6 * (((k1[i] + 2.0 * k2[i]) + 2.0 * k3[i]) + k4[i]);
+            // the four stages as a running weighted sum (w = 1, 2, 2, 1) and the next stage point x + c k (c = h/2, h/2, h)
+            for (int i = 0; i < NX; ++i) { t[i] = x[i]; S[i] = 0.0; }
+            for (int st = 0; st < 4; ++st) {
+                angles_sincos(t, s + 6 * st);
+                F::fc(t, uk, s + 6 * st, kk);
+                const real_t w = (st == 0 || st == 3) ? 1.0 : 2.0, c = st == 2 ? h : hh;
+                for (int i = 0; i < NX; ++i) { S[i] = S[i] + w * kk[i]; t[i] = x[i] + c * kk[i]; }
+            }
+            for (int i = 0; i < NX; ++i) traj[(k + 1) * NX + i] = x[i] = x[i] + h6 * S[i];
         }
         angles_sincos(x, &sc[24 * N]);
     }

@@ -87,14 +87,13 @@ struct Pantr {
     // box-constr-problem.hpp:59-64 ; returns h = 0
     __device__ __noinline__ void prox_grad_step_raw(double gamma, CVec xx, CVec g, Vec xh, Vec p) {
         ++st.ev_prox_grad_step;
-        for (int i = E::first(); i < n; i += E::STEP) {
+        E::map(n, [&](int i) {
             double xi = xx[i], s = -gamma * g[i];
             double lo = Model::C_lb(i) - xi, hi = Model::C_ub(i) - xi;
             double t  = s < lo ? lo : s;
             double pi = hi < t ? hi : t;
-            p[i]  = pi;
-            xh[i] = xi + pi;
-        }
+            return make_double2(pi, xi + pi);
+        }, [&](int i, double2 e) { p[i] = e.x; xh[i] = e.y; });
     }
     __device__ __noinline__ void eval_prox_grad_step(int s) { // pantr.tpp:88-92
         prox_grad_step_raw(it[s].gamma, X + s * n, G + s * n, XH + s * n, PP + s * n);

@@ -21,10 +21,11 @@
         const IVec J = JK;
         for (int i = E::first(); i < n; i += E::STEP) work[i] = 0.0;
         E::sync();
-        for (int j = E::first(); j < nJ; j += E::STEP) work[J[j]] = p[j];
+        struct IdxVal { int i; double v; };
+        E::map(nJ, [&](int j) { return IdxVal{J[j], p[j]}; }, [&](int, IdxVal e) { work[e.i] = e.v; });
         ++st.ev_hess_psi_prod;
         mdl.hess_psi_prod(xx, y, Sig, work, work2);
-        for (int j = E::first(); j < nJ; j += E::STEP) Bp[j] = work2[J[j]];
+        E::map(nJ, [&](int j) { return work2[J[j]]; }, [&](int j, double v) { Bp[j] = v; });
         E::sync();
     }
     // eval lambda of steihaugcg.hpp:62-65
@@ -45,7 +46,7 @@
     }
     // steihaugcg.hpp:39-117 ; g = rJ, step -> s (both compressed, length nJ)
     __device__ __noinline__ double steihaug(CVec xx, CVec g, int nJ, double radius, Vec s) {
-        for (int j = E::first(); j < nJ; j += E::STEP) { double gj = g[j]; z[j] = 0.0; r[j] = gj; d[j] = -gj; }
+        E::map(nJ, [&](int j) { return g[j]; }, [&](int j, double gj) { z[j] = 0.0; r[j] = gj; d[j] = -gj; });
         E::sync();
         double r_sq = xsqnorm<E>(r, nJ), grad_mag = xnorm2<E>(g, nJ);
         double tolerance = fmin(P.cg.tol_max,
@@ -61,11 +62,8 @@
                 double ta, tb;
                 boundaries(z, d, nJ, radius, ta, tb);
                 Vec pa = r, pb = d; // storage reuse as in the reference
-                for (int j = E::first(); j < nJ; j += E::STEP) {
-                    double zj = z[j], dj = d[j];
-                    pa[j] = zj + ta * dj;
-                    pb[j] = zj + tb * dj;
-                }
+                E::map(nJ, [&](int j) { return make_double2(z[j], d[j]); },
+                       [&](int j, double2 e) { pa[j] = e.x + ta * e.y; pb[j] = e.x + tb * e.y; }); // pa = r, pb = d: own index only
                 E::sync();
                 double q_a = cg_eval(xx, pa, g, nJ), q_b = cg_eval(xx, pb, g, nJ);
                 double q_min = fmin(q_a, q_b);
@@ -73,22 +71,23 @@
                 else              { xcopy<E>(s, pb, nJ); E::sync(); return q_b; }
             }
             double alpha = r_sq / dBd;
-            for (int j = E::first(); j < nJ; j += E::STEP) s[j] = z[j] + alpha * d[j];
+            E::map(nJ, [&](int j) { return z[j] + alpha * d[j]; }, [&](int j, double v) { s[j] = v; });
             E::sync();
             if (xnorm2<E>(s, nJ) >= radius) {
                 double ta, tb;
                 boundaries(z, d, nJ, radius, ta, tb);
-                for (int j = E::first(); j < nJ; j += E::STEP) s[j] = z[j] + tb * d[j];
+                E::map(nJ, [&](int j) { return z[j] + tb * d[j]; }, [&](int j, double v) { s[j] = v; });
                 E::sync();
                 return cg_eval(xx, s, g, nJ);
             }
-            for (int j = E::first(); j < nJ; j += E::STEP) r[j] = r[j] + alpha * Bd[j];
+            E::map(nJ, [&](int j) { return r[j] + alpha * Bd[j]; }, [&](int j, double v) { r[j] = v; });
             E::sync();
             double r_next_sq = xsqnorm<E>(r, nJ);
             if (sqrt(r_next_sq) < tolerance || i > max_iter) return cg_eval(xx, s, g, nJ);
             double beta_next = r_next_sq / r_sq;
             r_sq             = r_next_sq;
-            for (int j = E::first(); j < nJ; j += E::STEP) { d[j] = beta_next * d[j] - r[j]; z[j] = s[j]; }
+            E::map(nJ, [&](int j) { return make_double2(beta_next * d[j] - r[j], s[j]); },
+                   [&](int j, double2 e) { d[j] = e.x; z[j] = e.y; });
             E::sync();
             ++i;
         }
@@ -100,19 +99,20 @@
         nJ_out = nJ;
         const IVec J = JK, K = JK + nJ;
         const double mig = -1.0 / gamma;
-        for (int j = E::first(); j < nJ; j += E::STEP) { int i = J[j]; rJ[j] = mig * pk[i]; qk[i] = 0.0; }
-        for (int k = E::first(); k < nK; k += E::STEP) { int i = K[k]; qk[i] = pk[i]; }
+        struct IdxVal { int i; double v; };
+        E::map(nJ, [&](int j) { const int i = J[j]; return IdxVal{i, mig * pk[i]}; }, [&](int j, IdxVal e) { rJ[j] = e.v; qk[e.i] = 0.0; });
+        E::map(nK, [&](int k) { const int i = K[k]; return IdxVal{i, pk[i]}; }, [&](int, IdxVal e) { qk[e.i] = e.v; });
         double norm_qK_sq = E::sum(nK, [&](int k) { double pi = pk[K[k]]; return pi * pi; });
         E::sync();
         const double hvf = P.dir.hessian_vec_factor;
         if (hvf != 0) {
             ++st.ev_hess_psi_prod;
             mdl.hess_psi_prod(xx, y, Sig, qk, work);
-            for (int j = E::first(); j < nJ; j += E::STEP) rJ[j] = rJ[j] + work[J[j]] * hvf;
+            E::map(nJ, [&](int j) { return rJ[j] + work[J[j]] * hvf; }, [&](int j, double v) { rJ[j] = v; });
             E::sync();
         }
         double qJ_model = steihaug(xx, rJ, nJ, radius, qJ);
-        for (int j = E::first(); j < nJ; j += E::STEP) qk[J[j]] = qJ[j];
+        E::map(nJ, [&](int j) { return IdxVal{J[j], qJ[j]}; }, [&](int, IdxVal e) { qk[e.i] = e.v; });
         E::sync();
         return qJ_model - norm_qK_sq / (2 * gamma);
     }

@@ -195,7 +195,7 @@
             else if (q_model >= 0) ++st.direction_failures;
             if (q_model < 0) {
                 // compute_candidate_fbe: pantr.tpp:329-344
-                for (int i = E::first(); i < n; i += E::STEP) X[cand * n + i] = X[prox * n + i] + q[i];
+                E::map(n, [&](int i) { return X[prox * n + i] + q[i]; }, [&](int i, double v) { X[cand * n + i] = v; });
                 E::sync();
                 eval_psi_grad_psi(cand);
                 double pg = it[prox].gamma, pL = it[prox].L;

@@ -140,6 +140,7 @@ struct QuadCondensedModel {
     static constexpr int ABS = NV * qc::COL;            // doubles per step of ABv (a multiple of 2: 16-byte bulk copies)
     static constexpr int RING_SLOT = ABS + qc::ROW;     // doubles per ring slot
     static constexpr bool HAS_SCALE = true;
+    static constexpr int MAX_SMEM_SET = 0; // no solver vectors in shared memory: +2 % / +6 % with the L1 that leaves (r02_n_smem_sets.log)
     static constexpr bool OBJECTS_IN_SHARED = true; // solve kernel: model / solver objects in shared memory (pantr_b200.cu)
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int N) { return NC * (N + 1); }
@@ -216,27 +217,26 @@ struct QuadCondensedModel {
             s6[2 * a] = v.x; s6[2 * a + 1] = v.y;
         }
     }
-    /// (A rolled stage loop -- a quarter of the code, to relieve the instruction cache -- executed 50 % MORE warp
-    /// instructions (k / acc arrays through local memory, loop control) and was slower: profiles/r02_d_quadc_ncu_*.)
+    /// The four stages as ONE rolled loop over a running weighted sum S += w_s k_s (w = 1, 2, 2, 1; 0 + 1 k_1 = k_1) and the
+    /// next stage point t = x + c_s k_s (c = h/2, h/2, h): one stage of straight-line code (2.7 KB) instead of four.
+    /// Unrolled, the rollout loop body was 11.5 KB and its warps spent half of their stall samples waiting for
+    /// instructions (profiles/r02_k_quadc_ncu_regions.txt: no_inst 0.52); a first rolled version that kept k_1..k_4 in
+    /// arrays went through local memory and executed 50 % more instructions (profiles/r02_d_quadc_ncu_*).
     __device__ __forceinline__ static void rk4_step(double *x, const double *uk, double *sc_out) {
         using namespace qc;
-        double s6[6], t[NX], k1[NX], k2[NX], k3[NX], k4[NX];
-        stage_sincos(x, s6, sc_out, 0);
-        F::fc(x, uk, s6, k1);
+        double s6[6], t[NX], S[NX], k[NX];
 #pragma unroll
-        for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k1[i];
-        stage_sincos(t, s6, sc_out ? sc_out + 6 : nullptr, 1);
-        F::fc(t, uk, s6, k2);
+        for (int i = 0; i < NX; ++i) { t[i] = x[i]; S[i] = 0.0; }
+#pragma unroll 1
+        for (int st = 0; st < 4; ++st) {
+            stage_sincos(t, s6, sc_out ? sc_out + 6 * st : nullptr, st & 1);
+            F::fc(t, uk, s6, k);
+            const double w = (st == 0 || st == 3) ? 1.0 : 2.0, c = st == 2 ? h : hh;
 #pragma unroll
-        for (int i = 0; i < NX; ++i) t[i] = x[i] + hh * k2[i];
-        stage_sincos(t, s6, sc_out ? sc_out + 12 : nullptr, 0);
-        F::fc(t, uk, s6, k3);
+            for (int i = 0; i < NX; ++i) { S[i] = S[i] + w * k[i]; t[i] = x[i] + c * k[i]; }
+        }
 #pragma unroll
-        for (int i = 0; i < NX; ++i) t[i] = x[i] + h * k3[i];
-        stage_sincos(t, s6, sc_out ? sc_out + 18 : nullptr, 1);
-        F::fc(t, uk, s6, k4);
-#pragma unroll
-        for (int i = 0; i < NX; ++i) x[i] = x[i] + h6 * (((k1[i] + 2.0 * k2[i]) + 2.0 * k3[i]) + k4[i]);
+        for (int i = 0; i < NX; ++i) x[i] = x[i] + h6 * S[i];
     }
     /// Rollout (ss.py:24): fills traj and sc.
     __device__ __noinline__ void rollout(const double *u) {
