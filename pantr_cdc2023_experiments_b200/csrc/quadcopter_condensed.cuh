@@ -68,9 +68,19 @@ __host__ __device__ __forceinline__ double wx(int i, bool term) {
 __host__ __device__ __forceinline__ double wu(int j) { return j == 0 ? w_u : w_u + w_om; }
 __host__ __device__ __forceinline__ double sum_sq3(double a, double b, double c) { return (a * a + b * b) + c * c; }
 
-#define PANTR_QC_FNS(Name, ns)                                                                               \
+// resident warps per SM the solve kernel is compiled for: 16 (128 registers) for the simplified model, 12 (168 registers)
+// for the realistic one, whose generated derivative functions are twice as large (profiles/r02_o_variants.log: 16 -> 12
+// is -5 % for the simplified and +8 % for the realistic model in a two-wave run; 20 and 24 are slower for both)
+#ifndef PANTR_QC_MIN_BLOCKS
+#define PANTR_QC_MIN_BLOCKS 16
+#endif
+#ifndef PANTR_QC_MIN_BLOCKS_REALISTIC
+#define PANTR_QC_MIN_BLOCKS_REALISTIC 12
+#endif
+#define PANTR_QC_FNS(Name, ns, MB)                                                                             \
     struct Name {                                                                                            \
         static constexpr unsigned CONST_COLS = ns::FC_CONST_COLS;                                            \
+        static constexpr int MIN_BLOCKS = MB;                                                                \
         PANTR_HD static void fc(const double *x, const double *u, const double *sc, double *k) { ns::fc(x, u, sc, k); } \
         PANTR_HD static void fc_jvp(const double *x, const double *u, const double *sc, const double *dx,    \
                                     const double *du, double *dk) { ns::fc_jvp(x, u, sc, dx, du, dk); }      \
@@ -90,8 +100,8 @@ __host__ __device__ __forceinline__ double sum_sq3(double a, double b, double c)
         PANTR_HD static void con_hvjp(const double *x, const double *sc, const double *yh, const double *dx, \
                                       double *bx) { ns::con_hvjp(x, sc, yh, dx, bx); }                       \
     }
-PANTR_QC_FNS(SimpleFns, quadcopter_gen);
-PANTR_QC_FNS(RealisticFns, realistic_quadcopter_gen);
+PANTR_QC_FNS(SimpleFns, quadcopter_gen, PANTR_QC_MIN_BLOCKS);
+PANTR_QC_FNS(RealisticFns, realistic_quadcopter_gen, PANTR_QC_MIN_BLOCKS_REALISTIC);
 #undef PANTR_QC_FNS
 
 template <int count>
@@ -127,14 +137,11 @@ __device__ __forceinline__ StepRing step_ring() {
 }
 } // namespace qc
 
-#ifndef PANTR_QC_MIN_BLOCKS
-#define PANTR_QC_MIN_BLOCKS 16 // resident warps per SM the solve kernel is compiled for (128 registers)
-#endif
 
 template <class F>
 struct QuadCondensedModel {
     static constexpr int NX = qc::NX, NU = qc::NU, NC = qc::NC, NZ = qc::NZ;
-    static constexpr int MIN_BLOCKS = PANTR_QC_MIN_BLOCKS;
+    static constexpr int MIN_BLOCKS = F::MIN_BLOCKS;
     static constexpr unsigned VAR_COLS = ~F::CONST_COLS & 0x1fffu; // columns of AB that differ from step to step
     static constexpr int NV = __builtin_popcount(VAR_COLS), NCST = NZ - NV;
     static constexpr int ABS = NV * qc::COL;            // doubles per step of ABv (a multiple of 2: 16-byte bulk copies)

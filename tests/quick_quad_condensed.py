@@ -66,12 +66,12 @@ if what in ("all", "parity"):
             print(f"{name} N={N} B={B}: solve parity {'bit-exact' if good else 'FAILED'}; status {st['status'].tolist()} iters {st['inner_iterations'].tolist()}", flush=True)
     print("PARITY", "OK" if ok else "FAILED", flush=True)
 
-if what in ("all", "speed", "speed2", "speed3"):
+if what in ("all", "speed", "speed2", "speed3", "speed4"):
     scale = 0.1
     CAP = ["alm.max_iter=10", "solver.max_iter=100"]
     RUNS = ((("quadcopter", 60, 4736, "warp", CAP), ("realistic_quadcopter", 60, 4736, "warp", CAP), ("quadcopter", 60, 16384, "warp", []))
             if what == "speed2" else
-            (("quadcopter", 60, 4736, "warp", CAP), ("realistic_quadcopter", 60, 4736, "warp", CAP)) if what == "speed3" else None)
+            (("quadcopter", 60, 4736, "warp", CAP), ("realistic_quadcopter", 60, 4736, "warp", CAP)) if what == "speed3" else (("quadcopter", 60, 14208, "warp", CAP), ("realistic_quadcopter", 60, 14208, "warp", CAP)) if what == "speed4" else None)
     for name, N, B, mode, extra in RUNS or (("quadcopter", 60, 2368, "warp", CAP), ("quadcopter", 60, 4736, "warp", CAP),
                                     ("quadcopter", 60, 37888, "thread", CAP),
                                     ("quadcopter", 60, 4736, "warp", []),
