@@ -106,9 +106,9 @@ struct QuadcopterCondensed : Problem {
                 angles_sincos(t, s + 6 * st);
                 F::fc(t, uk, s + 6 * st, kk);
                 const real_t w = (st == 0 || st == 3) ? 1.0 : 2.0, c = st == 2 ? h : hh;
-                for (int i = 0; i < NX; ++i) { S[i] = S[i] + w * kk[i]; t[i] = x[i] + c * kk[i]; }
+                for (int i = 0; i < NX; ++i) { S[i] = std::fma(w, kk[i], S[i]); t[i] = std::fma(c, kk[i], x[i]); }
             }
-            for (int i = 0; i < NX; ++i) traj[(k + 1) * NX + i] = x[i] = x[i] + h6 * S[i];
+            for (int i = 0; i < NX; ++i) traj[(k + 1) * NX + i] = x[i] = std::fma(h6, S[i], x[i]);
         }
         angles_sincos(x, &sc[24 * N]);
     }

@@ -225,7 +225,7 @@ struct QuadCondensedModel {
         }
     }
     /// The four stages as ONE rolled loop over a running weighted sum S += w_s k_s (w = 1, 2, 2, 1; 0 + 1 k_1 = k_1) and the
-    /// next stage point t = x + c_s k_s (c = h/2, h/2, h): one stage of straight-line code (2.7 KB) instead of four.
+    /// next stage point t = x + c_s k_s (c = h/2, h/2, h), both as fma: one stage of straight-line code (2.7 KB) instead of four.
     /// Unrolled, the rollout loop body was 11.5 KB and its warps spent half of their stall samples waiting for
     /// instructions (profiles/r02_k_quadc_ncu_regions.txt: no_inst 0.52); a first rolled version that kept k_1..k_4 in
     /// arrays went through local memory and executed 50 % more instructions (profiles/r02_d_quadc_ncu_*).
@@ -240,10 +240,10 @@ struct QuadCondensedModel {
             F::fc(t, uk, s6, k);
             const double w = (st == 0 || st == 3) ? 1.0 : 2.0, c = st == 2 ? h : hh;
 #pragma unroll
-            for (int i = 0; i < NX; ++i) { S[i] = S[i] + w * k[i]; t[i] = x[i] + c * k[i]; }
+            for (int i = 0; i < NX; ++i) { S[i] = fma(w, k[i], S[i]); t[i] = fma(c, k[i], x[i]); } // (fma: +2.5 %, r02_q_variants.log)
         }
 #pragma unroll
-        for (int i = 0; i < NX; ++i) x[i] = x[i] + h6 * S[i];
+        for (int i = 0; i < NX; ++i) x[i] = fma(h6, S[i], x[i]);
     }
     /// Rollout (ss.py:24): fills traj and sc.
     __device__ __noinline__ void rollout(const double *u) {
@@ -383,6 +383,15 @@ struct QuadCondensedModel {
     /// product) with a per-lane coef (fma(1, b, a) is a + b exactly), so the x- and u-lanes share one code path.
     /// Step i (k = N-1-i) reads its record -- AB_k and row k -- from ring slot i % D, filled D steps earlier; slot,
     /// barrier, parity and exchange-buffer addresses are running registers (32-bit shared-window addresses).
+#ifndef PANTR_QC_ROWS_TMA
+#define PANTR_QC_ROWS_TMA 0
+#endif
+#ifndef PANTR_QC_SPLIT_CHAIN
+#define PANTR_QC_SPLIT_CHAIN 0
+#endif
+    __device__ __forceinline__ static void row_commit() { if (!PANTR_QC_ROWS_TMA) cp_async_commit_group(); }
+    template <int PENDING>
+    __device__ __forceinline__ static void row_wait() { if (!PANTR_QC_ROWS_TMA) cp_async_wait_group<PENDING>(); }
     __device__ __noinline__ void adjoint_recurrence(double *rows, double *out, bool grad, double cs) {
         using namespace qc;
         const int N = this->N;
@@ -402,11 +411,19 @@ struct QuadCondensedModel {
         double *dst = lane < NX ? rows + size_t(N - 1) * ROW + lane : out + size_t(N - 1) * NU + (cl - NX);
         const int dstride = lane < NX ? -ROW : -NU;
         auto refill = [&](int k, unsigned rec, unsigned bar) { // record of step k: ABv_k by lane 0 (TMA), the row by lanes 0..6 (cp.async)
+#if PANTR_QC_ROWS_TMA // A/B build: the row by TMA as well (needs the gpu-scope fence below, once per sweep); bit-identical, measured -0.4 % / -0.9 % (r02_q_variants.log): off
+            if (lane == 0) {
+                mbar_expect_tx_a(bar, (ABS + ROW) * 8);
+                bulk_g2s_a(rec, AB + size_t(k) * ABS, ABS * 8, bar);
+                bulk_g2s_a(rec + ABS * 8, rows + size_t(k) * ROW, ROW * 8, bar);
+            }
+#else
             if (lane == 0) {
                 mbar_expect_tx_a(bar, ABS * 8);
                 bulk_g2s_a(rec, AB + size_t(k) * ABS, ABS * 8, bar);
             }
             if (lane < ROW / 2) cp_async_16_a(rec + ABS * 8 + 16 * lane, rows + size_t(k) * ROW + 2 * lane);
+#endif
         };
         if (lane == 0) {
 #pragma unroll
@@ -415,13 +432,17 @@ struct QuadCondensedModel {
         }
         if (lane < NX) R.xch[lane] = rows[N * ROW + lane];
         for (int t = lane; t < NCST * COL; t += 32) R.cst[t] = this->ABc[t];
+#if PANTR_QC_ROWS_TMA
+        __threadfence();
+        proxy_async_fence();
+#endif
         __syncwarp(); // the rows the lanes have just written are ordered before the copies below
 #pragma unroll
         for (int i = 0; i < RING_D; ++i) {
             if (i < N) refill(N - 1 - i, slot0 + i * SLOT_B, bar0 + i * 8);
-            cp_async_commit_group();
+            row_commit();
         }
-        cp_async_wait_group<RING_D - 1>(); // step 0's row has landed ...
+        row_wait<RING_D - 1>(); // step 0's row has landed ...
         __syncwarp();                      // ... in every lane's view
         unsigned rec = slot0, bar = bar0, par = 0, xr = xch0, xw = xch0 + 128;
 #pragma unroll 1
@@ -431,23 +452,30 @@ struct QuadCondensedModel {
             lds_vec<NX>(is_var ? rec + voff : caddr, col);
             const double addend = lds_f64(rec + ABS * 8 + 8 * cl);
             lds_vec<NX>(xr, w);
+#if PANTR_QC_SPLIT_CHAIN // A/B build (changes the rounding): three chains of three instead of one of nine; measured +1.4 % / -0.4 % (r02_q_variants.log): off
+            const double a0 = fma(col[2], w[2], fma(col[1], w[1], col[0] * w[0]));
+            const double a1 = fma(col[5], w[5], fma(col[4], w[4], col[3] * w[3]));
+            const double a2 = fma(col[8], w[8], fma(col[7], w[7], col[6] * w[6]));
+            const double a = (a0 + a1) + a2;
+#else
             double a = col[0] * w[0];
 #pragma unroll
             for (int r = 1; r < NX; ++r) a = fma(col[r], w[r], a);
+#endif
             const double val = fma(coef, addend, a);
             if (lane < NX ? i + 1 < N : lane < NZ) *dst = val;
             dst += dstride;
             if (lane < NX) sts_f64(xw + 8 * lane, val);
-            cp_async_wait_group<RING_D - 2>(); // the next step's row has landed
+            row_wait<RING_D - 2>(); // the next step's row has landed
             __syncwarp();                      // slot `rec` has been read by every lane: refill it
             const int kn = N - 1 - RING_D - i;
             if (kn >= 0) refill(kn, rec, bar);
-            cp_async_commit_group();
+            row_commit();
             { const unsigned t = xr; xr = xw; xw = t; }
             rec += SLOT_B; bar += 8;
             if (rec == slot0 + RING_B) { rec = slot0; bar = bar0; par ^= 1u; }
         }
-        cp_async_wait_group<0>();
+        row_wait<0>();
     }
     /// Gradient of  s f + yh' g  wrt u (s = cost_scale); leaves lambda_1..N in lam.
     __device__ __noinline__ void adjoint(const double *u, double cost_scale, double *grad) {
@@ -522,9 +550,16 @@ struct QuadCondensedModel {
                 }
             }
             lds_vec<NZ>(xr, z);
+#if PANTR_QC_SPLIT_CHAIN
+            const double t0 = fma(row[4], z[4], fma(row[3], z[3], fma(row[2], z[2], fma(row[1], z[1], row[0] * z[0]))));
+            const double t1 = fma(row[8], z[8], fma(row[7], z[7], fma(row[6], z[6], row[5] * z[5])));
+            const double t2 = fma(row[12], z[12], fma(row[11], z[11], fma(row[10], z[10], row[9] * z[9])));
+            const double a = (t0 + t1) + t2;
+#else
             double a = row[0] * z[0];
 #pragma unroll
             for (int c = 1; c < NZ; ++c) a = fma(row[c], z[c], a);
+#endif
             dt += NX;
             if (lane < NX) { *dt = a; sts_f64(xw + 8 * lane, a); }
             if (lane < NU) sts_f64(xw + 8 * (NX + lane), vn);
