@@ -54,29 +54,29 @@ struct WarpExec {
         for (int i = lane_id(); i < n; i += 32) m = nanmax(m, f(i));
         return warp_nanmax(m);
     }
-    /// store(i, load(i)) for this lane's elements.  PANTR_MAP_BATCHED builds issue four elements' loads before the first
-    /// store (written as a plain loop, every store through a double* may alias the next element's operands, so the
-    /// compiler keeps load -> store -> load order).  Measured on one box (profiles/r02_m_variants.log): hanging chain
-    /// +1.2 %, quadcopters -3 % (larger code, more registers live) -- an A/B build variant, not the default.
+    /// store(i, load(i)) for this lane's elements.  BATCHED issues four elements' loads before the first store (written
+    /// as a plain loop, every store through a double* may alias the next element's operands, so the compiler keeps
+    /// load -> store -> load order).  Measured on one box (profiles/r02_m_variants.log): hanging chain +1.2 %, quadcopters
+    /// -3 % (larger code, more registers live), hence a per-model switch (Model::BATCHED_MAPS).
     /// load must not read what store writes at OTHER indices.
-    template <class L, class S>
+    template <bool BATCHED = false, class L, class S>
     __device__ static __forceinline__ void map(int n, L load, S store) {
-#if !defined(PANTR_MAP_BATCHED)
-        for (int i = lane_id(); i < n; i += 32) store(i, load(i));
-#else
-        for (int i = lane_id(); i < n; i += 128) {
-            const bool b1 = i + 32 < n, b2 = i + 64 < n, b3 = i + 96 < n;
-            const auto v0 = load(i);
-            auto v1 = v0, v2 = v0, v3 = v0;
-            if (b1) v1 = load(i + 32);
-            if (b2) v2 = load(i + 64);
-            if (b3) v3 = load(i + 96);
-            store(i, v0);
-            if (b1) store(i + 32, v1);
-            if (b2) store(i + 64, v2);
-            if (b3) store(i + 96, v3);
+        if constexpr (!BATCHED) {
+            for (int i = lane_id(); i < n; i += 32) store(i, load(i));
+        } else {
+            for (int i = lane_id(); i < n; i += 128) {
+                const bool b1 = i + 32 < n, b2 = i + 64 < n, b3 = i + 96 < n;
+                const auto v0 = load(i);
+                auto v1 = v0, v2 = v0, v3 = v0;
+                if (b1) v1 = load(i + 32);
+                if (b2) v2 = load(i + 64);
+                if (b3) v3 = load(i + 96);
+                store(i, v0);
+                if (b1) store(i + 32, v1);
+                if (b2) store(i + 64, v2);
+                if (b3) store(i + 96, v3);
+            }
         }
-#endif
     }
     /// ascending compaction of {i < n : pred(i)} into out[off..]; returns the count
     template <class F>
@@ -132,7 +132,7 @@ struct ThreadExec {
         for (int i = 0; i < n; ++i) m = nanmax(m, f(i));
         return m;
     }
-    template <class L, class S>
+    template <bool BATCHED = false, class L, class S>
     __device__ static __forceinline__ void map(int n, L load, S store) {
         for (int i = 0; i < n; ++i) store(i, load(i));
     }
@@ -168,9 +168,9 @@ __device__ __forceinline__ bool xall_finite(A a, int n) {
     for (int i = E::first(); i < n; i += E::STEP) ok = ok && isfinite(a[i]);
     return E::all(ok);
 }
-template <class E, class D, class S>
+template <class E, bool BATCHED = false, class D, class S>
 __device__ __forceinline__ void xcopy(D dst, S src, int n) {
-    E::map(n, [&](int i) { return src[i]; }, [&](int i, double v) { dst[i] = v; });
+    E::template map<BATCHED>(n, [&](int i) { return src[i]; }, [&](int i, double v) { dst[i] = v; });
 }
 
 } // namespace pantr

@@ -26,13 +26,13 @@
                                            double old_norm_e, CVec S_old, Vec S) {
         const auto &a = P.alm;
         const double theta = a.rel_penalty_increase_threshold;
-        if (norm_e <= a.dual_tolerance) { xcopy<E>(S, S_old, m); E::sync(); return; }
+        if (norm_e <= a.dual_tolerance) { xcopy<E, Model::BATCHED_MAPS>(S, S_old, m); E::sync(); return; }
         if (a.single_penalty_factor) {
             if (first_iter || norm_e > theta * old_norm_e) {
                 double new_S = fmin(a.max_penalty, Delta * S_old[0]);
                 E::sync();
                 for (int i = E::first(); i < m; i += E::STEP) S[i] = new_S;
-            } else xcopy<E>(S, S_old, m);
+            } else xcopy<E, Model::BATCHED_MAPS>(S, S_old, m);
         } else {
             for (int i = E::first(); i < m; i += E::STEP) {
                 if (first_iter || fabs(e[i]) > theta * fabs(old_e[i]))

@@ -78,6 +78,9 @@ struct Pantr {
         return size_t(WS_NVEC) * n + size_t(WS_MVEC) * m + (n + 1) / 2 + 2;
     }
 
+    /// element-wise vector loop of the execution policy, batched where the model asks for it (exec_policy.cuh)
+    template <class L, class S>
+    __device__ __forceinline__ void emap(int nn, L load, S store) const { E::template map<Model::BATCHED_MAPS>(nn, load, store); }
     // ---- problem function wrappers (+ counters, problem-with-counters.hpp:24-112) ----
     __device__ __noinline__ void eval_psi_grad_psi(int s) {
         ++st.ev_psi_grad_psi;
@@ -87,7 +90,7 @@ struct Pantr {
     // box-constr-problem.hpp:59-64 ; returns h = 0
     __device__ __noinline__ void prox_grad_step_raw(double gamma, CVec xx, CVec g, Vec xh, Vec p) {
         ++st.ev_prox_grad_step;
-        E::map(n, [&](int i) {
+        emap(n, [&](int i) {
             double xi = xx[i], s = -gamma * g[i];
             double lo = Model::C_lb(i) - xi, hi = Model::C_ub(i) - xi;
             double t  = s < lo ? lo : s;

@@ -22,10 +22,10 @@
         for (int i = E::first(); i < n; i += E::STEP) work[i] = 0.0;
         E::sync();
         struct IdxVal { int i; double v; };
-        E::map(nJ, [&](int j) { return IdxVal{J[j], p[j]}; }, [&](int, IdxVal e) { work[e.i] = e.v; });
+        emap(nJ, [&](int j) { return IdxVal{J[j], p[j]}; }, [&](int, IdxVal e) { work[e.i] = e.v; });
         ++st.ev_hess_psi_prod;
         mdl.hess_psi_prod(xx, y, Sig, work, work2);
-        E::map(nJ, [&](int j) { return work2[J[j]]; }, [&](int j, double v) { Bp[j] = v; });
+        emap(nJ, [&](int j) { return work2[J[j]]; }, [&](int j, double v) { Bp[j] = v; });
         E::sync();
     }
     // eval lambda of steihaugcg.hpp:62-65
@@ -46,7 +46,7 @@
     }
     // steihaugcg.hpp:39-117 ; g = rJ, step -> s (both compressed, length nJ)
     __device__ __noinline__ double steihaug(CVec xx, CVec g, int nJ, double radius, Vec s) {
-        E::map(nJ, [&](int j) { return g[j]; }, [&](int j, double gj) { z[j] = 0.0; r[j] = gj; d[j] = -gj; });
+        emap(nJ, [&](int j) { return g[j]; }, [&](int j, double gj) { z[j] = 0.0; r[j] = gj; d[j] = -gj; });
         E::sync();
         double r_sq = xsqnorm<E>(r, nJ), grad_mag = xnorm2<E>(g, nJ);
         double tolerance = fmin(P.cg.tol_max,
@@ -62,31 +62,31 @@
                 double ta, tb;
                 boundaries(z, d, nJ, radius, ta, tb);
                 Vec pa = r, pb = d; // storage reuse as in the reference
-                E::map(nJ, [&](int j) { return make_double2(z[j], d[j]); },
+                emap(nJ, [&](int j) { return make_double2(z[j], d[j]); },
                        [&](int j, double2 e) { pa[j] = e.x + ta * e.y; pb[j] = e.x + tb * e.y; }); // pa = r, pb = d: own index only
                 E::sync();
                 double q_a = cg_eval(xx, pa, g, nJ), q_b = cg_eval(xx, pb, g, nJ);
                 double q_min = fmin(q_a, q_b);
-                if (q_a == q_min) { xcopy<E>(s, pa, nJ); E::sync(); return q_a; }
-                else              { xcopy<E>(s, pb, nJ); E::sync(); return q_b; }
+                if (q_a == q_min) { xcopy<E, Model::BATCHED_MAPS>(s, pa, nJ); E::sync(); return q_a; }
+                else              { xcopy<E, Model::BATCHED_MAPS>(s, pb, nJ); E::sync(); return q_b; }
             }
             double alpha = r_sq / dBd;
-            E::map(nJ, [&](int j) { return z[j] + alpha * d[j]; }, [&](int j, double v) { s[j] = v; });
+            emap(nJ, [&](int j) { return z[j] + alpha * d[j]; }, [&](int j, double v) { s[j] = v; });
             E::sync();
             if (xnorm2<E>(s, nJ) >= radius) {
                 double ta, tb;
                 boundaries(z, d, nJ, radius, ta, tb);
-                E::map(nJ, [&](int j) { return z[j] + tb * d[j]; }, [&](int j, double v) { s[j] = v; });
+                emap(nJ, [&](int j) { return z[j] + tb * d[j]; }, [&](int j, double v) { s[j] = v; });
                 E::sync();
                 return cg_eval(xx, s, g, nJ);
             }
-            E::map(nJ, [&](int j) { return r[j] + alpha * Bd[j]; }, [&](int j, double v) { r[j] = v; });
+            emap(nJ, [&](int j) { return r[j] + alpha * Bd[j]; }, [&](int j, double v) { r[j] = v; });
             E::sync();
             double r_next_sq = xsqnorm<E>(r, nJ);
             if (sqrt(r_next_sq) < tolerance || i > max_iter) return cg_eval(xx, s, g, nJ);
             double beta_next = r_next_sq / r_sq;
             r_sq             = r_next_sq;
-            E::map(nJ, [&](int j) { return make_double2(beta_next * d[j] - r[j], s[j]); },
+            emap(nJ, [&](int j) { return make_double2(beta_next * d[j] - r[j], s[j]); },
                    [&](int j, double2 e) { d[j] = e.x; z[j] = e.y; });
             E::sync();
             ++i;
@@ -100,19 +100,19 @@
         const IVec J = JK, K = JK + nJ;
         const double mig = -1.0 / gamma;
         struct IdxVal { int i; double v; };
-        E::map(nJ, [&](int j) { const int i = J[j]; return IdxVal{i, mig * pk[i]}; }, [&](int j, IdxVal e) { rJ[j] = e.v; qk[e.i] = 0.0; });
-        E::map(nK, [&](int k) { const int i = K[k]; return IdxVal{i, pk[i]}; }, [&](int, IdxVal e) { qk[e.i] = e.v; });
+        emap(nJ, [&](int j) { const int i = J[j]; return IdxVal{i, mig * pk[i]}; }, [&](int j, IdxVal e) { rJ[j] = e.v; qk[e.i] = 0.0; });
+        emap(nK, [&](int k) { const int i = K[k]; return IdxVal{i, pk[i]}; }, [&](int, IdxVal e) { qk[e.i] = e.v; });
         double norm_qK_sq = E::sum(nK, [&](int k) { double pi = pk[K[k]]; return pi * pi; });
         E::sync();
         const double hvf = P.dir.hessian_vec_factor;
         if (hvf != 0) {
             ++st.ev_hess_psi_prod;
             mdl.hess_psi_prod(xx, y, Sig, qk, work);
-            E::map(nJ, [&](int j) { return rJ[j] + work[J[j]] * hvf; }, [&](int j, double v) { rJ[j] = v; });
+            emap(nJ, [&](int j) { return rJ[j] + work[J[j]] * hvf; }, [&](int j, double v) { rJ[j] = v; });
             E::sync();
         }
         double qJ_model = steihaug(xx, rJ, nJ, radius, qJ);
-        E::map(nJ, [&](int j) { return IdxVal{J[j], qJ[j]}; }, [&](int, IdxVal e) { qk[e.i] = e.v; });
+        emap(nJ, [&](int j) { return IdxVal{J[j], qJ[j]}; }, [&](int, IdxVal e) { qk[e.i] = e.v; });
         E::sync();
         return qJ_model - norm_qK_sq / (2 * gamma);
     }

@@ -77,7 +77,7 @@
         res = InnerResult{PANTR_B200_BUSY, INFINITY, 0};
         s.always_overwrite = always_overwrite; s.has_errz = has_errz;
         if constexpr (Model::HAS_ROLLOUT_TAG) mdl.untag(); // the iterate slots are about to be overwritten
-        xcopy<E>(X + curr * n, x, n); // pantr.tpp:195
+        xcopy<E, Model::BATCHED_MAPS>(X + curr * n, x, n); // pantr.tpp:195
         E::sync();
         // ---- initial Lipschitz estimate: pantr.tpp:200-217, panoc-helpers.tpp:288-334 ----
         if (pp.Lipschitz.L_0 <= 0) {
@@ -153,7 +153,7 @@
                     if (has_errz) errz[i] = (1.0 / Sig[i]) * (yhi - y[i]);
                     y[i] = yhi;
                 }
-                xcopy<E>(x, XH + curr * n, n);
+                xcopy<E, Model::BATCHED_MAPS>(x, XH + curr * n, n);
             }
             st.final_gamma = it[curr].gamma; st.final_psi = it[curr].psi_xh;
             st.final_h = it[curr].h; st.final_fbe = fbe(curr);
@@ -165,7 +165,7 @@
         // Unless the stop criterion already needed it, the reference evaluates grad_L(x_hat, y_hat) here and
         // immediately overwrites the result with psi_grad_psi(prox.x): numerically dead, so only counted.
         if (!need_grad) ++st.ev_grad_L;
-        xcopy<E>(X + prox * n, XH + curr * n, n);
+        xcopy<E, Model::BATCHED_MAPS>(X + prox * n, XH + curr * n, n);
         if constexpr (Model::HAS_ROLLOUT_TAG) mdl.retag(XH + curr * n, X + prox * n); // psi(x_hat) rolled this very point out
         double cg_ = it[curr].gamma, cL_ = it[curr].L, cpsi = it[curr].psi_xh;
         E::sync();
@@ -195,7 +195,7 @@
             else if (q_model >= 0) ++st.direction_failures;
             if (q_model < 0) {
                 // compute_candidate_fbe: pantr.tpp:329-344
-                E::map(n, [&](int i) { return X[prox * n + i] + q[i]; }, [&](int i, double v) { X[cand * n + i] = v; });
+                emap(n, [&](int i) { return X[prox * n + i] + q[i]; }, [&](int i, double v) { X[cand * n + i] = v; });
                 E::sync();
                 eval_psi_grad_psi(cand);
                 double pg = it[prox].gamma, pL = it[prox].L;

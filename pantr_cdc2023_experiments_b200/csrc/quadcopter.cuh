@@ -16,6 +16,7 @@ struct QuadcopterModel {
     using CVec = typename E::CVec;
     static constexpr int NX = quad::NX, NU = quad::NU, NC = quad::NC;
     static constexpr bool HAS_ROLLOUT_TAG = false;
+    static constexpr bool BATCHED_MAPS = false;
     static constexpr int MIN_BLOCKS = 8; // resident warps per SM the solve kernel is compiled for
     using Gen = G;
     __host__ __device__ static int n(int N) { return NU * N; }

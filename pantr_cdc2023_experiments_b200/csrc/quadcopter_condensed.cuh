@@ -148,6 +148,7 @@ struct QuadCondensedModel {
     static constexpr int RING_SLOT = ABS + qc::ROW;     // doubles per ring slot
     static constexpr bool HAS_SCALE = true;
     static constexpr int MAX_SMEM_SET = 0; // no solver vectors in shared memory: +2 % / +6 % with the L1 that leaves (r02_n_smem_sets.log)
+    static constexpr bool BATCHED_MAPS = false; // solver vector loops stay plain (-3 % batched, exec_policy.cuh)
     static constexpr bool OBJECTS_IN_SHARED = true; // solve kernel: model / solver objects in shared memory (pantr_b200.cu)
     __host__ __device__ static int n(int N) { return NU * N; }
     __host__ __device__ static int m(int N) { return NC * (N + 1); }
