@@ -532,9 +532,16 @@ def run_b200(args):
     traffic, traffic_src = None, None
     tfile = os.path.join(ROOT, "profiles", "traffic.json")
     lib_sha = hashlib.sha256(open(_lib.LIB_PATH, "rb").read()).hexdigest()
+    # a rebuild of the same sources may not reproduce the .so byte for byte: the capture also records a hash of the sources
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    try:
+        from source_hash import source_sha256
+        src_sha = source_sha256()
+    except Exception:
+        src_sha = None
     if os.path.exists(tfile):
         for tj in json.load(open(tfile)).get("captures", []):
-            if (tj.get("lib_sha256") == lib_sha and tj.get("problem") == dom.name and tj.get("batch") == dom.B
+            if ((tj.get("lib_sha256") == lib_sha or tj.get("src_sha256") == src_sha) and tj.get("problem") == dom.name and tj.get("batch") == dom.B
                     and tj.get("horizon") == dom.N and tj.get("start") == ("warm" if args.config == "hanging_chain" else "cold")):
                 traffic, traffic_src = tj["dram_bytes_per_launch"], tj.get("source")
     kname = {"hanging_chain": "solve_kernel<HangingChain>", "quadcopter": "solve_kernel<QuadCondensedModel<SimpleFns>>",

@@ -28,7 +28,13 @@ def gb(name):
 
 rd, wr = gb("dram__bytes_read.sum"), gb("dram__bytes_write.sum")
 lib = os.path.join(ROOT, "pantr_cdc2023_experiments_b200", "libpantr_b200.so")
-entry = {"lib_sha256": hashlib.sha256(open(lib, "rb").read()).hexdigest(), "problem": problem, "batch": batch, "horizon": horizon,
+
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from source_hash import source_sha256  # noqa: E402
+
+
+entry = {"lib_sha256": hashlib.sha256(open(lib, "rb").read()).hexdigest(), "src_sha256": source_sha256(), "problem": problem, "batch": batch, "horizon": horizon,
          "start": start, "kernel": vals[col["Kernel Name"]], "dram_bytes_per_launch": rd + wr, "dram_bytes_read": rd,
          "dram_bytes_write": wr, "kernel_ms_under_ncu": float(vals[col["gpu__time_duration.sum"]]) * {"ms": 1.0, "us": 1e-3, "s": 1e3, "ns": 1e-6}[units[col["gpu__time_duration.sum"]]],
          "source": source}
