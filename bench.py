@@ -507,7 +507,9 @@ def run_b200(args):
             conv += int((st["status"] == 1).sum())
         return tt, conv
 
-    e2e_step()  # warm-up (allocates the staging buffers)
+    e2e_warmup = total_ms / args.steps < 5000.0  # a step of several seconds does not notice the one-off staging allocation
+    if e2e_warmup:
+        e2e_step()  # warm-up (allocates the staging buffers)
     barrier()
     e2e_t, e2e_conv = 0.0, 0
     for _ in range(e2e_steps):
@@ -601,12 +603,17 @@ def run_b200(args):
         for s, (x0n, uin, _, _) in zip(segs, host):
             Sp = min(s.B, cores if s.name != "hanging_chain" else 4 * cores)
             us, sts, _ = cpu_solve_batch(ou.load(), PROBLEMS[s.name][1], s.N, s.par, x0n[:Sp], uin[:Sp], s.prob.m, cores)
-            rel = np.abs(us - s.u_dev[:Sp]).max() / max(1.0, np.abs(us).max())
+            # instances the device ended with MaxTime (alm.max_time on the device clock; the oracle has no clock) are
+            # timing dependent and cannot be compared: counted, not checked
+            keep = np.asarray(s.stats["status"][:Sp]) != 2
+            ud, st_d, it_d = s.u_dev[:Sp][keep], np.asarray(s.stats["status"][:Sp])[keep], np.asarray(s.stats["inner_iterations"][:Sp])[keep]
+            uo, st_o, it_o = us[keep], sts[keep, 0], sts[keep, 2]
+            rel = np.abs(uo - ud).max() / max(1.0, np.abs(uo).max()) if keep.any() else 0.0
             parity["segments"].append({
-                "problem": s.name, "horizon": s.N, "instances": Sp, "max_rel_err_u": float(rel),
-                "bitwise_equal_u": bool(np.array_equal(us, s.u_dev[:Sp])),
-                "status_equal": bool((sts[:, 0] == s.stats["status"][:Sp]).all()),
-                "max_iter_diff": int(np.abs(sts[:, 2] - s.stats["inner_iterations"][:Sp]).max())})
+                "problem": s.name, "horizon": s.N, "instances": int(keep.sum()), "excluded_max_time": int((~keep).sum()),
+                "max_rel_err_u": float(rel), "bitwise_equal_u": bool(np.array_equal(uo, ud)),
+                "status_equal": bool((st_o == st_d).all()),
+                "max_iter_diff": int(np.abs(it_o - it_d).max()) if keep.any() else 0})
         parity["all_bitwise_equal"] = all(p["bitwise_equal_u"] and p["status_equal"] and p["max_iter_diff"] == 0
                                           for p in parity["segments"])
 
@@ -652,7 +659,8 @@ def run_b200(args):
             "mean_hess_psi_prod": float(np.mean(np.concatenate([s.stats["ev_hess_psi_prod"] for s in segs]))),
             "cold_solve": cold_info,
             "e2e": {"value": e2e_value, "unit": "solves/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "bitwise_equal_to_device_path": same_as_device},
+                    "d2h_bytes_per_step": d2h, "steps": e2e_steps, "warmup_steps": int(e2e_warmup),
+                    "bitwise_equal_to_device_path": same_as_device},
             "gpu_launches": int(launches), "grid": dom.solver.grid_size(dom.prob),
             "per_rank": ranks, "stats_gather_ok": gathered_ok,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "parity_check": parity,

@@ -5,4 +5,3 @@ timeout 900 python -m pytest tests/test_gpu_sharded.py -m gpu -q > gpurun_out/r0
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1"
 timeout 900 $TR --master-port 29511 bench.py --gpus 2 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r02s_bench_2gpu_weak.json 2> gpurun_out/r02s_bench_2gpu_weak.err; echo "weak rc=$?"; grep '"metric"' gpurun_out/r02s_bench_2gpu_weak.json | cut -c1-400
 timeout 900 $TR --master-port 29512 bench.py --gpus 2 --steps 3 --warmup 3 --no-cpu-baseline --shard global --batch 32768 > gpurun_out/r02s_bench_2gpu_global.json 2> gpurun_out/r02s_bench_2gpu_global.err; echo "global rc=$?"; grep '"metric"' gpurun_out/r02s_bench_2gpu_global.json | cut -c1-400
-timeout 900 $TR --master-port 29513 bench.py --gpus 2 --config quadcopter --batch 8192 --steps 1 --warmup 1 --no-cpu-baseline --shard global > gpurun_out/r02s_bench_2gpu_quadcopter_global.json 2> gpurun_out/r02s_bench_2gpu_quadcopter.err; echo "quad global rc=$?"; grep '"metric"' gpurun_out/r02s_bench_2gpu_quadcopter_global.json | cut -c1-400
