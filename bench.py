@@ -169,14 +169,15 @@ def workload_text(args):
         f"{segs[0][0]} N={segs[0][1]}..{segs[-1][1]} ({len(segs)} horizons) x {segs[0][2]} each"
     start = "warm-started (cold solve, plant step, shift; the warm solve is timed)" if args.config == "hanging_chain" else "cold start"
     quad = "" if args.config == "hanging_chain" else f"; quadcopter x0 = nominal + {args.scale} * (p +-0.1, v +-0.5, theta +-0.2)"
-    return f"{per} per GPU, {start}{quad} (BASELINE.json configs[{CONFIGS[args.config]['index']}])"
+    scope = "per GPU" if args.shard == "weak" else "in ONE global batch sharded over the GPUs by instance index"
+    return f"{per} {scope}, {start}{quad} (BASELINE.json configs[{CONFIGS[args.config]['index']}])"
 
 
 def config_dict(args, world, sample=None):
     segs = segments_of(args)
     d = {"workload": workload_text(args), "config": args.config,
-         "segments": [{"problem": n, "horizon": N, "batch_per_gpu": B} for n, N, B in segs],
-         "batch_per_gpu": sum(B for _, _, B in segs),
+         "segments": [{"problem": n, "horizon": N, "batch_per_gpu": B if args.shard == "weak" else round(B / world, 1)} for n, N, B in segs],
+         "batch_per_gpu": sum(B for _, _, B in segs) if args.shard == "weak" else round(sum(B for _, _, B in segs) / world, 1),
          "global_batch": sum(B for _, _, B in segs) * (world if args.shard == "weak" else 1),
          "x0_scale": None if args.config == "hanging_chain" else args.scale,
          "parallelism": f"instances sharded by index over {world} GPU(s) ({args.shard}), no collective on the data path",
