@@ -98,3 +98,35 @@ def test_shard_ranges_cover_batch():
         r = [sharding.shard_range(B, k, W) for k in range(W)]
         assert r[0][0] == 0 and r[-1][1] == B
         assert all(a[1] == b[0] for a, b in zip(r[:-1], r[1:])) and all(lo <= hi for lo, hi in r)
+
+
+def test_traffic_json_is_keyed_by_library_and_source_hash():
+    """profiles/traffic.json (tools/make_traffic.py): every capture names the library AND the sources it was taken from;
+    bench.py reports roofline.traffic only for a matching build."""
+    import json
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "tools"))
+    from source_hash import source_sha256
+    caps = json.load(open(os.path.join(root, "profiles", "traffic.json")))["captures"]
+    assert caps
+    for c in caps:
+        assert len(c["lib_sha256"]) == 64 and len(c["src_sha256"]) == 64
+        assert c["dram_bytes_per_launch"] == c["dram_bytes_read"] + c["dram_bytes_write"]
+        assert {"problem", "batch", "horizon", "start", "source"} <= set(c)
+    assert len(source_sha256()) == 64 and source_sha256() == source_sha256()
+
+
+def test_bench_config_of_a_globally_sharded_batch():
+    import argparse
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    a = argparse.Namespace(config="hanging_chain", batch=32768, horizon=60, horizons="", scale=0.1, shard="global")
+    d = bench.config_dict(a, 2)
+    assert d["global_batch"] == 32768 and d["batch_per_gpu"] == 16384 and "ONE global batch" in d["workload"]
+    a.shard = "weak"
+    d = bench.config_dict(a, 2)
+    assert d["global_batch"] == 65536 and d["batch_per_gpu"] == 32768 and "per GPU" in d["workload"]
